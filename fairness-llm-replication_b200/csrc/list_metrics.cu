@@ -1,0 +1,482 @@
+// List similarity of every (user, variant) list against the user's neutral list:
+// Jaccard (src/utils.py:224-239), SERP* and PRAG* (oracle/np_oracle.py:list_metrics).
+//
+// Table kernel (the fast path): one thread per (user, variant) pair, one CTA per tile of T
+// users.  A tile's lists, lengths and neutral lists are contiguous in HBM and are staged
+// with one-dimensional bulk TMA copies (cp.async.bulk + mbarrier).  Per user slot a
+// `vocab`-entry byte table maps item id -> rank in the neutral list (0xFF = absent);
+// per thread a private `vocab`-bit set (word-interleaved across threads, so every access is
+// bank-conflict free) collapses duplicates exactly as the reference's set() does.  PRAG*'s
+// pair count is a running 64-bit mask of neutral ranks already seen: one __popcll per item.
+//
+// Compare kernel: vocabulary-independent O(K^2) fallback for shapes the table kernel does
+// not cover (V = 1 pair lists of the string API, huge vocabularies, K > 64 Jaccard-only).
+#include <algorithm>
+
+#include "common.cuh"
+
+using namespace flr;
+
+namespace {
+
+constexpr int NT = 128;                 // threads per CTA (table kernel)
+constexpr int kTableSmemBudget = 110 * 1024;   // keeps two CTAs resident per SM
+
+struct LmParams {
+    const int32_t *neutral, *neutral_len, *lists, *lens;
+    int64_t U;
+    int V, K, k_cap, vocab, empty_policy;
+    int T, use_bulk, vocab_pad, W;
+    int32_t *out_inter, *out_union;
+    float *out_jac, *out_serp, *out_prag;
+    double *partial;
+    int32_t *status;
+};
+
+struct LmSmem {
+    size_t off_lists, off_neutral, off_lens, off_nlen, off_na, off_tab, off_bits, total;
+};
+
+__host__ __device__ inline size_t align16(size_t x) { return (x + 15) & ~static_cast<size_t>(15); }
+
+__host__ __device__ inline LmSmem lm_layout(int T, int V, int K, int vocab_pad, int W) {
+    LmSmem s;
+    size_t o = 16;                                   // mbarrier
+    s.off_lists = o;   o = align16(o + static_cast<size_t>(T) * V * K * 4);
+    s.off_neutral = o; o = align16(o + static_cast<size_t>(T) * K * 4);
+    s.off_lens = o;    o = align16(o + static_cast<size_t>(T) * V * 4);
+    s.off_nlen = o;    o = align16(o + static_cast<size_t>(T) * 4);
+    s.off_na = o;      o = align16(o + static_cast<size_t>(T) * 4);
+    s.off_tab = o;     o = align16(o + static_cast<size_t>(T) * vocab_pad);
+    s.off_bits = o;    o = align16(o + static_cast<size_t>(W) * NT * 4);
+    s.total = o;
+    return s;
+}
+
+template <int VEC>
+__device__ __forceinline__ void load_ids(const int32_t *p, int (&ids)[VEC]) {
+    if constexpr (VEC == 4) {
+        int4 q = *reinterpret_cast<const int4 *>(p);
+        ids[0] = q.x; ids[1] = q.y; ids[2] = q.z; ids[3] = q.w;
+    } else if constexpr (VEC == 2) {
+        int2 q = *reinterpret_cast<const int2 *>(p);
+        ids[0] = q.x; ids[1] = q.y;
+    } else {
+        ids[0] = *p;
+    }
+}
+
+template <int VEC, bool RANK>
+__global__ void __launch_bounds__(NT, 2) list_metrics_table_kernel(const LmParams p) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    const LmSmem L = lm_layout(p.T, p.V, p.K, p.vocab_pad, p.W);
+    uint64_t *bar = reinterpret_cast<uint64_t *>(smem);
+    int32_t *s_lists = reinterpret_cast<int32_t *>(smem + L.off_lists);
+    int32_t *s_neutral = reinterpret_cast<int32_t *>(smem + L.off_neutral);
+    int32_t *s_lens = reinterpret_cast<int32_t *>(smem + L.off_lens);
+    int32_t *s_nlen = reinterpret_cast<int32_t *>(smem + L.off_nlen);
+    int32_t *s_na = reinterpret_cast<int32_t *>(smem + L.off_na);
+    uint8_t *s_tab = smem + L.off_tab;
+    uint32_t *s_bits = reinterpret_cast<uint32_t *>(smem + L.off_bits);
+
+    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    const int V = p.V, K = p.K, T = p.T, Kn = p.k_cap;
+    const unsigned vocab = static_cast<unsigned>(p.vocab);
+    const int pairs_per_tile = T * V;
+    const int slot = t / V;
+    const bool pair_thread = t < pairs_per_tile;
+
+    {   // one-time init: tables to "absent", private bit sets to empty
+        int4 *tab4 = reinterpret_cast<int4 *>(s_tab);
+        const int n4 = T * p.vocab_pad / 16;
+        for (int i = t; i < n4; i += NT) tab4[i] = make_int4(-1, -1, -1, -1);
+        for (int w = 0; w < p.W; ++w) s_bits[w * NT + t] = 0u;
+        if (t == 0) {
+            mbar_init(bar, 1);
+            fence_mbar_init();
+        }
+    }
+    __syncthreads();
+
+    uint32_t phase = 0;
+    double acc_j = 0.0;
+    long long acc_s = 0, acc_p = 0;
+    int acc_n = 0, oov = 0;
+    const int64_t n_tiles = (p.U + T - 1) / T;
+    const uint32_t bytes_lists = static_cast<uint32_t>(T) * V * K * 4, bytes_neutral = static_cast<uint32_t>(T) * K * 4;
+    const uint32_t bytes_lens = static_cast<uint32_t>(T) * V * 4, bytes_nlen = static_cast<uint32_t>(T) * 4;
+
+    for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        const int64_t u0 = tile * T;
+        const int tu = static_cast<int>(min(static_cast<int64_t>(T), p.U - u0));
+
+        // ---- stage the tile ----
+        if (p.use_bulk && tu == T) {
+            if (t == 0) {
+                fence_proxy_async();
+                mbar_expect_tx(bar, bytes_lists + bytes_neutral + bytes_lens + bytes_nlen);
+                bulk_g2s(s_lists, p.lists + u0 * V * K, bytes_lists, bar);
+                bulk_g2s(s_neutral, p.neutral + u0 * K, bytes_neutral, bar);
+                bulk_g2s(s_lens, p.lens + u0 * V, bytes_lens, bar);
+                bulk_g2s(s_nlen, p.neutral_len + u0, bytes_nlen, bar);
+            }
+            mbar_wait(bar, phase);
+            phase ^= 1u;
+        } else {
+            const int32_t *gl = p.lists + u0 * V * K;
+            for (int i = t; i < tu * V * K; i += NT) s_lists[i] = gl[i];
+            const int32_t *gn = p.neutral + u0 * K;
+            for (int i = t; i < tu * K; i += NT) s_neutral[i] = gn[i];
+            for (int i = t; i < tu * V; i += NT) s_lens[i] = p.lens[u0 * V + i];
+            for (int i = t; i < tu; i += NT) s_nlen[i] = p.neutral_len[u0 + i];
+            __syncthreads();
+        }
+
+        // ---- rank tables: tab[id] = first position of id in the neutral list ----
+        for (int s = warp; s < tu; s += NT / 32) {
+            const int Ka = max(0, min(s_nlen[s], Kn));
+            const int32_t *A = s_neutral + s * K;
+            uint8_t *tab = s_tab + s * p.vocab_pad;
+            for (int base = ((Ka - 1) >> 5) << 5; base >= 0; base -= 32) {   // later halves first
+                const int j = base + lane;
+                if (j < Ka) {
+                    const unsigned id = static_cast<unsigned>(A[j]);
+                    if (id < vocab) tab[id] = static_cast<uint8_t>(j); else ++oov;
+                }
+                __syncwarp();
+            }
+            bool again;
+            do {    // duplicates inside one 32-wide step raced: let the smallest position win
+                again = false;
+                for (int base = 0; base < Ka; base += 32) {
+                    const int j = base + lane;
+                    if (j < Ka) {
+                        const unsigned id = static_cast<unsigned>(A[j]);
+                        if (id < vocab && tab[id] > j) { tab[id] = static_cast<uint8_t>(j); again = true; }
+                    }
+                }
+                __syncwarp();
+                again = __any_sync(0xffffffffu, again);
+            } while (again);
+            int cnt = 0;
+            for (int base = 0; base < Ka; base += 32) {
+                const int j = base + lane;
+                bool first = false;
+                if (j < Ka) {
+                    const unsigned id = static_cast<unsigned>(A[j]);
+                    first = id < vocab && tab[id] == j;
+                }
+                cnt += __popc(__ballot_sync(0xffffffffu, first));
+            }
+            if (lane == 0) s_na[s] = cnt;
+        }
+        __syncthreads();
+
+        // ---- one thread per pair ----
+        if (pair_thread && slot < tu) {
+            const int Kb = max(0, min(s_lens[t], Kn));
+            const int32_t *row = s_lists + t * K;
+            const uint8_t *tab = s_tab + slot * p.vocab_pad;
+            uint32_t *mybits = s_bits + t;
+            uint64_t seen = 0;
+            int n_b = 0, inter = 0, serp = 0, prag = 0;
+            for (int j0 = 0; j0 < Kb; j0 += VEC) {
+                int ids[VEC];
+                load_ids<VEC>(row + j0, ids);
+#pragma unroll
+                for (int e = 0; e < VEC; ++e) {
+                    const int j = j0 + e;
+                    const unsigned id = static_cast<unsigned>(ids[e]);
+                    if (j < Kb) {
+                        if (id < vocab) {
+                            uint32_t *wp = mybits + (id >> 5) * NT;
+                            const uint32_t w = *wp, b = 1u << (id & 31u);
+                            if (!(w & b)) {
+                                *wp = w | b;
+                                ++n_b;
+                                const unsigned r = tab[id];
+                                if (r != 0xFFu) {
+                                    ++inter;
+                                    if constexpr (RANK) {
+                                        serp += Kn - j;
+                                        prag += __popcll(seen & ((1ull << r) - 1ull));
+                                        seen |= 1ull << r;
+                                    }
+                                } else if constexpr (RANK) {
+                                    prag += __popcll(seen);   // r = +inf: every earlier hit outranks it
+                                }
+                            }
+                        } else {
+                            ++oov;
+                        }
+                    }
+                }
+            }
+            const int n_a = s_na[slot];
+            const int uni = n_a + n_b - inter;
+            double jac;
+            if (p.empty_policy == FLR_EMPTY_BOTH_IS_ONE)
+                jac = uni > 0 ? static_cast<double>(inter) / static_cast<double>(uni) : 1.0;
+            else
+                jac = (n_a == 0 || n_b == 0) ? 0.0 : static_cast<double>(inter) / static_cast<double>(uni);
+            const int64_t pair = u0 * V + t;
+            if (p.out_inter) p.out_inter[pair] = inter;
+            if (p.out_union) p.out_union[pair] = uni;
+            if (p.out_jac) p.out_jac[pair] = static_cast<float>(jac);
+            if constexpr (RANK) {
+                if (p.out_serp) p.out_serp[pair] = static_cast<float>(serp) / static_cast<float>(Kn * (Kn + 1) / 2);
+                if (p.out_prag) p.out_prag[pair] = static_cast<float>(prag) / static_cast<float>(Kn * (Kn + 1));
+            }
+            acc_j += jac;
+            acc_s += serp;
+            acc_p += prag;
+            acc_n += 1;
+            // wipe the private bit set for the next tile
+            for (int j0 = 0; j0 < Kb; j0 += VEC) {
+                int ids[VEC];
+                load_ids<VEC>(row + j0, ids);
+#pragma unroll
+                for (int e = 0; e < VEC; ++e) {
+                    const unsigned id = static_cast<unsigned>(ids[e]);
+                    if (j0 + e < Kb && id < vocab) mybits[(id >> 5) * NT] = 0u;
+                }
+            }
+        }
+        __syncthreads();
+
+        // ---- un-mark the rank tables ----
+        for (int s = warp; s < tu; s += NT / 32) {
+            const int Ka = max(0, min(s_nlen[s], Kn));
+            const int32_t *A = s_neutral + s * K;
+            uint8_t *tab = s_tab + s * p.vocab_pad;
+            for (int j = lane; j < Ka; j += 32) {
+                const unsigned id = static_cast<unsigned>(A[j]);
+                if (id < vocab) tab[id] = 0xFFu;
+            }
+        }
+        __syncthreads();
+    }
+
+    double *dst = p.partial + (static_cast<size_t>(blockIdx.x) * NT + t) * 4;
+    dst[0] = acc_j;
+    dst[1] = static_cast<double>(acc_s);
+    dst[2] = static_cast<double>(acc_p);
+    dst[3] = static_cast<double>(acc_n);
+    if (oov && p.status) atomicAdd(p.status, oov);
+}
+
+// Fixed-order reduction of the per-thread partials: thread v sums (block, slot) ascending.
+__global__ void list_metrics_finalize_kernel(const double *__restrict__ partial, int grid, int threads,
+                                             int T, int V, double *__restrict__ out) {
+    const int v = blockIdx.x * blockDim.x + threadIdx.x;
+    if (v >= V) return;
+    double a0 = 0, a1 = 0, a2 = 0, a3 = 0;
+    for (int b = 0; b < grid; ++b)
+        for (int s = 0; s < T; ++s) {
+            const double *q = partial + (static_cast<size_t>(b) * threads + s * V + v) * 4;
+            a0 += q[0]; a1 += q[1]; a2 += q[2]; a3 += q[3];
+        }
+    out[v * 4 + 0] = a0; out[v * 4 + 1] = a1; out[v * 4 + 2] = a2; out[v * 4 + 3] = a3;
+}
+
+// ---------------------------------------------------------------------------------------
+// Compare kernel: thread per pair, rows read straight from global memory.
+// ---------------------------------------------------------------------------------------
+constexpr int CMP_THREADS = 128;
+
+template <bool RANK>
+__global__ void __launch_bounds__(CMP_THREADS) list_metrics_cmp_kernel(const LmParams p) {
+    const int V = p.V, K = p.K, Kn = p.k_cap;
+    const int64_t total = p.U * V;
+    const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;   // multiple of V by construction
+    const int64_t first = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+    double acc_j = 0.0;
+    long long acc_s = 0, acc_p = 0;
+    int acc_n = 0, oov = 0;
+    const bool check_vocab = p.vocab > 0;
+    const unsigned vocab = static_cast<unsigned>(p.vocab);
+    for (int64_t pair = first; pair < total; pair += stride) {
+        const int64_t u = pair / V;
+        const int32_t *A = p.neutral + u * K;
+        const int32_t *B = p.lists + pair * K;
+        const int Ka = max(0, min(p.neutral_len[u], Kn));
+        const int Kb = max(0, min(p.lens[pair], Kn));
+        int n_a = 0;
+        for (int i = 0; i < Ka; ++i) {
+            const int x = A[i];
+            if (check_vocab && static_cast<unsigned>(x) >= vocab) { ++oov; continue; }
+            bool dup = false;
+            for (int i2 = 0; i2 < i; ++i2) dup |= (A[i2] == x);
+            n_a += !dup;
+        }
+        uint64_t seen = 0;
+        int n_b = 0, inter = 0, serp = 0, prag = 0;
+        for (int j = 0; j < Kb; ++j) {
+            const int x = B[j];
+            if (check_vocab && static_cast<unsigned>(x) >= vocab) { ++oov; continue; }
+            bool dup = false;
+            for (int j2 = 0; j2 < j; ++j2) dup |= (B[j2] == x);
+            if (dup) continue;
+            ++n_b;
+            int r = -1;
+            for (int i = Ka - 1; i >= 0; --i) r = (A[i] == x) ? i : r;      // first occurrence
+            if (r >= 0) {
+                ++inter;
+                if constexpr (RANK) {
+                    serp += Kn - j;
+                    prag += __popcll(seen & ((1ull << r) - 1ull));
+                    seen |= 1ull << r;
+                }
+            } else if constexpr (RANK) {
+                prag += __popcll(seen);
+            }
+        }
+        const int uni = n_a + n_b - inter;
+        double jac;
+        if (p.empty_policy == FLR_EMPTY_BOTH_IS_ONE)
+            jac = uni > 0 ? static_cast<double>(inter) / static_cast<double>(uni) : 1.0;
+        else
+            jac = (n_a == 0 || n_b == 0) ? 0.0 : static_cast<double>(inter) / static_cast<double>(uni);
+        if (p.out_inter) p.out_inter[pair] = inter;
+        if (p.out_union) p.out_union[pair] = uni;
+        if (p.out_jac) p.out_jac[pair] = static_cast<float>(jac);
+        if constexpr (RANK) {
+            if (p.out_serp) p.out_serp[pair] = static_cast<float>(serp) / static_cast<float>(Kn * (Kn + 1) / 2);
+            if (p.out_prag) p.out_prag[pair] = static_cast<float>(prag) / static_cast<float>(Kn * (Kn + 1));
+        }
+        acc_j += jac; acc_s += serp; acc_p += prag; acc_n += 1;
+    }
+    double *dst = p.partial + static_cast<size_t>(first) * 4;
+    dst[0] = acc_j;
+    dst[1] = static_cast<double>(acc_s);
+    dst[2] = static_cast<double>(acc_p);
+    dst[3] = static_cast<double>(acc_n);
+    if (oov && p.status) atomicAdd(p.status, oov);
+}
+
+// thread v sums the partials of all threads whose first pair has variant v (index = v mod V)
+__global__ void list_metrics_cmp_finalize_kernel(const double *__restrict__ partial, int64_t n_threads, int V,
+                                                 double *__restrict__ out) {
+    const int v = blockIdx.x * blockDim.x + threadIdx.x;
+    if (v >= V) return;
+    double a0 = 0, a1 = 0, a2 = 0, a3 = 0;
+    for (int64_t i = v; i < n_threads; i += V) {
+        const double *q = partial + i * 4;
+        a0 += q[0]; a1 += q[1]; a2 += q[2]; a3 += q[3];
+    }
+    out[v * 4 + 0] = a0; out[v * 4 + 1] = a1; out[v * 4 + 2] = a2; out[v * 4 + 3] = a3;
+}
+
+struct Plan {
+    bool table;
+    int T, vocab_pad, W, grid;
+    size_t smem;
+    int64_t cmp_threads;
+};
+
+Plan make_plan(int64_t U, int V, int K, int k_cap, int vocab) {
+    Plan pl{};
+    const int sms = device_sm_count();
+    pl.vocab_pad = (vocab + 15) & ~15;
+    pl.W = (vocab + 31) / 32;
+    pl.table = false;
+    if (vocab > 0 && vocab <= 16384 && k_cap <= FLR_MAX_RANK_K && V >= 2 && V <= NT) {
+        int T = NT / V;
+        if (T >= 4) T &= ~3;                 // multiples of 4 keep every bulk copy 16-byte sized
+        while (T >= 1 && lm_layout(T, V, K, pl.vocab_pad, pl.W).total > static_cast<size_t>(kTableSmemBudget))
+            T = (T > 4) ? ((T - 1) & ~3) : T - 1;
+        if (T >= 1 && T * V * 2 >= NT) {      // at least half of the CTA's threads own a pair
+            pl.table = true;
+            pl.T = T;
+            pl.smem = lm_layout(T, V, K, pl.vocab_pad, pl.W).total;
+            const int64_t tiles = (U + T - 1) / T;
+            pl.grid = static_cast<int>(std::min<int64_t>(std::max<int64_t>(tiles, 1), 2LL * sms));
+        }
+    }
+    if (!pl.table) {
+        // grid*threads is a multiple of V so a thread keeps one variant over its whole stride
+        int64_t want = std::min<int64_t>(std::max<int64_t>(U * V, 1), 16LL * sms * CMP_THREADS);
+        int64_t blocks = (want + CMP_THREADS - 1) / CMP_THREADS;
+        blocks = ((blocks + V - 1) / V) * V;
+        pl.grid = static_cast<int>(blocks);
+        pl.cmp_threads = blocks * CMP_THREADS;
+    }
+    return pl;
+}
+
+}  // namespace
+
+extern "C" size_t flr_list_metrics_scratch_bytes(int64_t U, int V, int K, int vocab) {
+    if (U < 0 || V < 1 || K < 1) return 0;
+    // covers both kernels for any k_cap: table partials (<= 2*SMs CTAs) or compare partials
+    const int sms = device_sm_count();
+    size_t table = static_cast<size_t>(2) * sms * NT * 4 * sizeof(double);
+    int64_t want = std::min<int64_t>(std::max<int64_t>(U * V, 1), 16LL * sms * CMP_THREADS);
+    int64_t blocks = (want + CMP_THREADS - 1) / CMP_THREADS;
+    blocks = ((blocks + V - 1) / V) * V;
+    size_t cmp = static_cast<size_t>(blocks) * CMP_THREADS * 4 * sizeof(double);
+    (void)K; (void)vocab;
+    return std::max(table, cmp);
+}
+
+extern "C" int flr_list_metrics(const int32_t *neutral, const int32_t *neutral_len, const int32_t *lists,
+                                const int32_t *lens, int64_t U, int V, int K, int k_cap, int vocab,
+                                int empty_policy, int rank_metrics, int32_t *out_inter, int32_t *out_union,
+                                float *out_jac, float *out_serp, float *out_prag, double *out_variant_sums,
+                                int32_t *out_status, void *scratch, size_t scratch_bytes, void *stream_) {
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    FLR_REQUIRE(U >= 0 && V >= 1 && K >= 1, FLR_E_INVALID, "list_metrics: need U>=0, V>=1, K>=1");
+    FLR_REQUIRE(k_cap >= 1, FLR_E_INVALID, "list_metrics: k_cap must be >= 1");
+    FLR_REQUIRE(empty_policy == FLR_EMPTY_ANY_IS_ZERO || empty_policy == FLR_EMPTY_BOTH_IS_ONE, FLR_E_INVALID,
+                "list_metrics: unknown empty_policy %d", empty_policy);
+    if (k_cap > K) k_cap = K;
+    FLR_REQUIRE(!rank_metrics || k_cap <= FLR_MAX_RANK_K, FLR_E_UNSUPPORTED,
+                "list_metrics: SERP*/PRAG* need k_cap <= %d (got %d)", FLR_MAX_RANK_K, k_cap);
+    FLR_REQUIRE(U * V < (1LL << 40), FLR_E_UNSUPPORTED, "list_metrics: too many pairs");
+    if (U == 0) {
+        if (out_variant_sums) FLR_CUDA(cudaMemsetAsync(out_variant_sums, 0, sizeof(double) * 4 * V, stream));
+        return FLR_OK;
+    }
+    FLR_REQUIRE(neutral && neutral_len && lists && lens, FLR_E_INVALID, "list_metrics: null input pointer");
+    FLR_REQUIRE(scratch && scratch_bytes >= flr_list_metrics_scratch_bytes(U, V, K, vocab), FLR_E_SCRATCH,
+                "list_metrics: scratch too small (%zu < %zu)", scratch_bytes,
+                flr_list_metrics_scratch_bytes(U, V, K, vocab));
+
+    const Plan pl = make_plan(U, V, K, k_cap, vocab);
+    LmParams p{};
+    p.neutral = neutral; p.neutral_len = neutral_len; p.lists = lists; p.lens = lens;
+    p.U = U; p.V = V; p.K = K; p.k_cap = k_cap; p.vocab = vocab; p.empty_policy = empty_policy;
+    p.out_inter = out_inter; p.out_union = out_union; p.out_jac = out_jac;
+    p.out_serp = out_serp; p.out_prag = out_prag;
+    p.partial = static_cast<double *>(scratch);
+    p.status = out_status;
+    p.vocab_pad = pl.vocab_pad; p.W = pl.W;
+
+    if (pl.table) {
+        p.T = pl.T;
+        p.use_bulk = (pl.T % 4 == 0) && aligned16(neutral) && aligned16(neutral_len) && aligned16(lists) &&
+                     aligned16(lens);
+        const int vec = (K % 4 == 0) ? 4 : (K % 2 == 0) ? 2 : 1;
+        void (*kern)(const LmParams) = nullptr;
+        if (rank_metrics) kern = vec == 4 ? list_metrics_table_kernel<4, true> : vec == 2 ? list_metrics_table_kernel<2, true> : list_metrics_table_kernel<1, true>;
+        else              kern = vec == 4 ? list_metrics_table_kernel<4, false> : vec == 2 ? list_metrics_table_kernel<2, false> : list_metrics_table_kernel<1, false>;
+        FLR_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(pl.smem)));
+        kern<<<pl.grid, NT, pl.smem, stream>>>(p);
+        FLR_LAUNCH_CHECK("list_metrics_table_kernel");
+        if (out_variant_sums) {
+            list_metrics_finalize_kernel<<<(V + 127) / 128, 128, 0, stream>>>(p.partial, pl.grid, NT, pl.T, V,
+                                                                               out_variant_sums);
+            FLR_LAUNCH_CHECK("list_metrics_finalize_kernel");
+        }
+    } else {
+        if (rank_metrics) list_metrics_cmp_kernel<true><<<pl.grid, CMP_THREADS, 0, stream>>>(p);
+        else              list_metrics_cmp_kernel<false><<<pl.grid, CMP_THREADS, 0, stream>>>(p);
+        FLR_LAUNCH_CHECK("list_metrics_cmp_kernel");
+        if (out_variant_sums) {
+            list_metrics_cmp_finalize_kernel<<<(V + 127) / 128, 128, 0, stream>>>(p.partial, pl.cmp_threads, V,
+                                                                                   out_variant_sums);
+            FLR_LAUNCH_CHECK("list_metrics_cmp_finalize_kernel");
+        }
+    }
+    return FLR_OK;
+}

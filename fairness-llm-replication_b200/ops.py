@@ -1,0 +1,325 @@
+"""Tensor-level entry points over the C ABI (include/flr_b200.h).
+
+PyTorch is used for device memory, streams and (in ``pipeline``) ``torch.distributed``
+only; every computation below is one of the library's own sm_100a kernels, launched on the
+current CUDA stream.  Nothing here synchronises unless stated.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass
+from typing import Optional
+
+import numpy as np
+import torch
+
+from . import _lib
+from ._lib import (DTYPE_F32, DTYPE_F64, EMPTY_ANY_IS_ZERO, EMPTY_BOTH_IS_ONE, MAX_ROUNDS,
+                   SELECT_BINS, SELECT_STATE_WORDS)
+
+__all__ = [
+    "list_metrics", "ListMetrics", "pair_jaccard", "cosine_nonconformity", "radix_select",
+    "threshold_schedule", "violation_detect", "conformal_keep_len", "normalize_rows_bf16",
+    "pair_similarity", "synth_lists", "synth_embeddings", "synth_lists_host",
+    "synth_embeddings_host", "zipf_cdf_host", "device_info",
+    "EMPTY_ANY_IS_ZERO", "EMPTY_BOTH_IS_ONE",
+]
+
+
+def _ptr(t: Optional[torch.Tensor]):
+    return None if t is None else C.c_void_p(t.data_ptr())
+
+
+def _stream():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _dev(t: torch.Tensor, dtype, name: str) -> torch.Tensor:
+    if not isinstance(t, torch.Tensor) or not t.is_cuda:
+        raise TypeError(f"{name} must be a CUDA tensor (this path has no CPU implementation)")
+    if t.dtype != dtype:
+        raise TypeError(f"{name} must be {dtype}, got {t.dtype}")
+    if not t.is_contiguous():
+        raise ValueError(f"{name} must be contiguous")
+    return t
+
+
+_scratch = {}
+
+
+def _workspace(device, nbytes: int) -> torch.Tensor:
+    """Per-device scratch, grown on demand and reused by later calls on the same stream order."""
+    key = (device.type, device.index)
+    buf = _scratch.get(key)
+    if buf is None or buf.numel() < nbytes:
+        buf = torch.empty(max(nbytes, 1 << 20), dtype=torch.uint8, device=device)
+        _scratch[key] = buf
+    return buf
+
+
+def device_info():
+    sm, maj, mnr = C.c_int(), C.c_int(), C.c_int()
+    _lib.call("flr_device_info", C.byref(sm), C.byref(maj), C.byref(mnr))
+    return {"sm_count": sm.value, "cc": (maj.value, mnr.value)}
+
+
+# ------------------------------------------------------------------------------ list metrics
+@dataclass
+class ListMetrics:
+    inter: torch.Tensor                  # int32 [U, V]  |A & B|, exact
+    union: Optional[torch.Tensor]        # int32 [U, V]  |A | B|, exact
+    jaccard: torch.Tensor                # float32 [U, V]
+    serp: Optional[torch.Tensor]         # float32 [U, V]
+    prag: Optional[torch.Tensor]         # float32 [U, V]
+    variant_sums: Optional[torch.Tensor]  # float64 [V, 4]: sum jaccard, sum serp_num, sum prag_num, users
+    status: torch.Tensor                 # int32 [1]: ids found outside [0, vocab)
+    k_cap: int
+
+    def variant_means(self) -> torch.Tensor:
+        """float64 [V, 3]: mean Jaccard, SERP*, PRAG* per variant (divides the exact sums)."""
+        s = self.variant_sums
+        n = s[:, 3:4].clamp_min(1.0)
+        kn = float(self.k_cap)
+        scale = torch.tensor([1.0, 1.0 / (kn * (kn + 1) / 2.0), 1.0 / (kn * (kn + 1.0))],
+                             dtype=torch.float64, device=s.device)
+        return s[:, :3] / n * scale
+
+
+def list_metrics(neutral, neutral_len, lists, lens, *, vocab: int, k_cap: Optional[int] = None,
+                 empty_policy: int = EMPTY_BOTH_IS_ONE, rank_metrics: bool = True,
+                 want_union: bool = False, want_sums: bool = True) -> ListMetrics:
+    """Jaccard / SERP* / PRAG* of lists[u, v, :] against neutral[u, :]  (flr_list_metrics).
+
+    neutral int32 [U, K], neutral_len int32 [U], lists int32 [U, V, K], lens int32 [U, V].
+    """
+    lists = _dev(lists, torch.int32, "lists")
+    if lists.dim() != 3:
+        raise ValueError("lists must be [U, V, K]")
+    U, V, K = lists.shape
+    neutral = _dev(neutral, torch.int32, "neutral")
+    neutral_len = _dev(neutral_len, torch.int32, "neutral_len")
+    lens = _dev(lens, torch.int32, "lens")
+    if tuple(neutral.shape) != (U, K) or neutral_len.numel() != U or lens.numel() != U * V:
+        raise ValueError("shape mismatch between neutral/neutral_len/lists/lens")
+    k_cap = K if k_cap is None else int(k_cap)
+    dev = lists.device
+    inter = torch.empty((U, V), dtype=torch.int32, device=dev)
+    union = torch.empty((U, V), dtype=torch.int32, device=dev) if want_union else None
+    jac = torch.empty((U, V), dtype=torch.float32, device=dev)
+    serp = torch.empty((U, V), dtype=torch.float32, device=dev) if rank_metrics else None
+    prag = torch.empty((U, V), dtype=torch.float32, device=dev) if rank_metrics else None
+    sums = torch.empty((V, 4), dtype=torch.float64, device=dev) if want_sums else None
+    status = torch.zeros(1, dtype=torch.int32, device=dev)
+    nbytes = _lib.load().flr_list_metrics_scratch_bytes(U, V, K, vocab)
+    ws = _workspace(dev, nbytes)
+    _lib.call("flr_list_metrics", _ptr(neutral), _ptr(neutral_len), _ptr(lists), _ptr(lens),
+              U, V, K, k_cap, int(vocab), int(empty_policy), int(bool(rank_metrics)),
+              _ptr(inter), _ptr(union), _ptr(jac), _ptr(serp), _ptr(prag), _ptr(sums), _ptr(status),
+              _ptr(ws), ws.numel(), _stream())
+    return ListMetrics(inter, union, jac, serp, prag, sums, status, min(k_cap, K))
+
+
+def pair_jaccard(lists, lens, *, vocab: int):
+    """All-pairs intersections among each user's M lists: int32 [U, M, M], sizes int32 [U, M]."""
+    lists = _dev(lists, torch.int32, "lists")
+    U, M, K = lists.shape
+    lens = _dev(lens, torch.int32, "lens")
+    inter = torch.empty((U, M, M), dtype=torch.int32, device=lists.device)
+    sizes = torch.empty((U, M), dtype=torch.int32, device=lists.device)
+    _lib.call("flr_pair_jaccard", _ptr(lists), _ptr(lens), U, M, K, int(vocab), _ptr(inter), _ptr(sizes),
+              _stream())
+    return inter, sizes
+
+
+# ------------------------------------------------------------------------------ conformal
+def cosine_nonconformity(a, b, *, hist0: Optional[torch.Tensor] = None, out=None) -> torch.Tensor:
+    """s[u, v] = max(0, 1 - cos(a[u], b[u, v]));  a float32 [U, D], b float32 [U, V, D] (or [U, D]).
+
+    ``hist0`` (int64 [2048], zeroed by the caller) receives the pass-0 select histogram."""
+    a = _dev(a, torch.float32, "a")
+    b = _dev(b, torch.float32, "b")
+    squeeze = b.dim() == 2
+    if squeeze:
+        b = b.unsqueeze(1)
+    U, V, D = b.shape
+    if tuple(a.shape) != (U, D):
+        raise ValueError("a must be [U, D] matching b [U, V, D]")
+    if out is None:
+        out = torch.empty((U, V), dtype=torch.float32, device=a.device)
+    else:
+        _dev(out, torch.float32, "out")
+    if hist0 is not None:
+        _dev(hist0, torch.int64, "hist0")
+        if hist0.numel() != SELECT_BINS:
+            raise ValueError("hist0 must hold 2048 int64 bins")
+    _lib.call("flr_cosine_nonconformity", _ptr(a), _ptr(b), U, V, D, _ptr(out), _ptr(hist0), _stream())
+    return out.squeeze(1) if squeeze else out
+
+
+def radix_select(scores, *, alpha: float = 0.1, groups: Optional[torch.Tensor] = None, n_groups: int = 1,
+                 k: Optional[torch.Tensor] = None, hist0: Optional[torch.Tensor] = None,
+                 all_reduce=None):
+    """Exact per-group order statistic at the reference's conformal index
+    (src/phase3_facter_mitigation.py:165-178).  Returns (thresholds [G], state int64 [G, 8]).
+
+    ``scores`` float32 or float64 (any shape), ``groups`` uint8 ids (same numel) or None.
+    ``hist0``: a pass-0 histogram already built (cosine kernel), skips the first read.
+    ``all_reduce``: callable applied to each pass's int64 histogram before it is scanned
+    (multi-GPU: sum over ranks); the result is then the order statistic of the union.
+    """
+    if scores.dtype == torch.float32:
+        dtype = DTYPE_F32
+    elif scores.dtype == torch.float64:
+        dtype = DTYPE_F64
+    else:
+        raise TypeError("scores must be float32 or float64")
+    scores = _dev(scores, scores.dtype, "scores")
+    N = scores.numel()
+    G = int(n_groups)
+    dev = scores.device
+    if groups is not None:
+        groups = _dev(groups, torch.uint8, "groups")
+        if groups.numel() != N:
+            raise ValueError("groups must have one id per score")
+    elif G != 1:
+        raise ValueError("n_groups > 1 needs group ids")
+    n_pass = _lib.load().flr_select_num_passes(dtype)
+    hist = torch.zeros((n_pass, G, SELECT_BINS), dtype=torch.int64, device=dev)
+    state = torch.zeros((G, SELECT_STATE_WORDS), dtype=torch.int64, device=dev)
+    thr = torch.empty(G, dtype=scores.dtype, device=dev)
+    if k is not None:
+        k = _dev(k, torch.int64, "k")
+    for p in range(n_pass):
+        h = hist[p]
+        if p == 0 and hist0 is not None:
+            if G != 1:
+                raise ValueError("a fused pass-0 histogram exists only for one group")
+            h = hist0.view(1, SELECT_BINS)
+        else:
+            _lib.call("flr_select_hist", _ptr(scores), dtype, _ptr(groups), N, G, p, _ptr(state), _ptr(h),
+                      _stream())
+        if all_reduce is not None:
+            all_reduce(h)
+        _lib.call("flr_select_scan", dtype, G, p, float(1 - alpha), _ptr(k), _ptr(h), _ptr(state), _ptr(thr),
+                  _stream())
+    return thr, state
+
+
+def threshold_schedule(q0, state, *, gamma: float = 0.95, q_min: float = 0.0, rounds: int = 4):
+    """thr[0..rounds] of the round-synchronous update (oracle/np_oracle.py:threshold_schedule)."""
+    q0 = _dev(q0, torch.float32, "q0")
+    state = _dev(state, torch.int64, "state")
+    thr = torch.empty(rounds + 1, dtype=torch.float32, device=q0.device)
+    _lib.call("flr_threshold_schedule", _ptr(q0), _ptr(state), float(gamma), float(q_min), int(rounds), _ptr(thr),
+              _stream())
+    return thr
+
+
+def violation_detect(scores, thr, *, rounds: int, n_variants: int = 1, per_variant: bool = True,
+                     counts: Optional[torch.Tensor] = None, variant_counts: Optional[torch.Tensor] = None):
+    """flags[i] bit r = scores[i] > thr[r]; returns (flags uint8, counts int64 [R], variant_counts
+    int64 [V, R] or None).  Counters are added to when passed in."""
+    scores = _dev(scores, torch.float32, "scores")
+    thr = _dev(thr, torch.float32, "thr")
+    if thr.numel() < rounds:
+        raise ValueError("thr must hold at least `rounds` thresholds")
+    dev = scores.device
+    flags = torch.empty(scores.shape, dtype=torch.uint8, device=dev)
+    if counts is None:
+        counts = torch.zeros(rounds, dtype=torch.int64, device=dev)
+    if per_variant and variant_counts is None:
+        variant_counts = torch.zeros((n_variants, rounds), dtype=torch.int64, device=dev)
+    _lib.call("flr_violation_detect", _ptr(scores), scores.numel(), int(n_variants), _ptr(thr), int(rounds),
+              _ptr(flags), _ptr(counts), _ptr(variant_counts if per_variant else None), _stream())
+    return flags, counts, (variant_counts if per_variant else None)
+
+
+def conformal_keep_len(lens, thr, groups: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """Prefix length kept by apply_conformal_filtering (src/phase3_facter_mitigation.py:205-216)."""
+    lens = _dev(lens, torch.int32, "lens")
+    thr = _dev(thr, torch.float64, "thr")
+    if groups is not None:
+        groups = _dev(groups, torch.uint8, "groups")
+    out = torch.empty(lens.shape, dtype=torch.int32, device=lens.device)
+    _lib.call("flr_conformal_keep_len", _ptr(lens), _ptr(groups), _ptr(thr), lens.numel(), _ptr(out), _stream())
+    return out
+
+
+# ------------------------------------------------------------------------------ config 4
+def normalize_rows_bf16(x) -> torch.Tensor:
+    x = _dev(x, torch.float32, "x")
+    D = x.shape[-1]
+    out = torch.empty(x.shape, dtype=torch.bfloat16, device=x.device)
+    _lib.call("flr_normalize_rows_bf16", _ptr(x), x.numel() // D, D, _ptr(out), _stream())
+    return out
+
+
+def pair_similarity(x_bf16) -> torch.Tensor:
+    """S[u] = X[u] X[u]^T, x bf16 [U, M, D] -> float32 [U, M, M] (tcgen05 / TMEM / TMA)."""
+    x = _dev(x_bf16, torch.bfloat16, "x_bf16")
+    U, M, D = x.shape
+    out = torch.empty((U, M, M), dtype=torch.float32, device=x.device)
+    nbytes = _lib.load().flr_pair_similarity_scratch_bytes(U, M, D)
+    ws = _workspace(x.device, nbytes)
+    _lib.call("flr_pair_similarity_gemm", _ptr(x), U, M, D, _ptr(out), _ptr(ws), ws.numel(), _stream())
+    return out
+
+
+# ------------------------------------------------------------------------------ synthetic inputs
+_cdf_cache = {}
+
+
+def zipf_cdf_host(vocab: int) -> np.ndarray:
+    cdf = _cdf_cache.get(vocab)
+    if cdf is None:
+        cdf = np.empty(vocab, np.float32)
+        _lib.call("flr_synth_zipf_cdf_host", cdf.ctypes.data_as(C.c_void_p), int(vocab))
+        _cdf_cache[vocab] = cdf
+    return cdf
+
+
+def synth_lists_host(seed: int, user0: int, U: int, V: int, K: int, vocab: int):
+    """numpy (neutral [U,K], neutral_len [U], lists [U,V,K], lens [U,V]); runs on host cores."""
+    cdf = zipf_cdf_host(vocab)
+    neutral = np.empty((U, K), np.int32)
+    nlen = np.empty((U,), np.int32)
+    lists = np.empty((U, V, K), np.int32)
+    lens = np.empty((U, V), np.int32)
+    p = lambda a: a.ctypes.data_as(C.c_void_p)
+    _lib.call("flr_synth_lists_host", int(seed), int(user0), U, V, K, int(vocab), p(cdf), p(neutral), p(nlen),
+              p(lists), p(lens))
+    return neutral, nlen, lists, lens
+
+
+def synth_embeddings_host(seed: int, user0: int, U: int, V: int, D: int):
+    en = np.empty((U, D), np.float32)
+    e = np.empty((U, V, D), np.float32)
+    p = lambda a: a.ctypes.data_as(C.c_void_p)
+    _lib.call("flr_synth_embeddings_host", int(seed), int(user0), U, V, D, p(en), p(e))
+    return en, e
+
+
+def synth_lists(seed: int, user0: int, U: int, V: int, K: int, vocab: int, device):
+    device = torch.device(device)
+    cdf = torch.from_numpy(zipf_cdf_host(vocab)).to(device)
+    neutral = torch.empty((U, K), dtype=torch.int32, device=device)
+    nlen = torch.empty((U,), dtype=torch.int32, device=device)
+    lists = torch.empty((U, V, K), dtype=torch.int32, device=device)
+    lens = torch.empty((U, V), dtype=torch.int32, device=device)
+    with torch.cuda.device(device):
+        _lib.call("flr_synth_lists", int(seed), int(user0), U, V, K, int(vocab), _ptr(cdf), _ptr(neutral),
+                  _ptr(nlen), _ptr(lists), _ptr(lens), _stream())
+        torch.cuda.current_stream().synchronize()      # cdf is freed on return
+    return neutral, nlen, lists, lens
+
+
+def synth_embeddings(seed: int, user0: int, U: int, V: int, D: int, device, chunk_users: int = 1 << 16):
+    device = torch.device(device)
+    en = torch.empty((U, D), dtype=torch.float32, device=device)
+    e = torch.empty((U, V, D), dtype=torch.float32, device=device)
+    with torch.cuda.device(device):
+        for s in range(0, U, chunk_users):
+            n = min(chunk_users, U - s)
+            _lib.call("flr_synth_embeddings", int(seed), int(user0 + s), n, V, D, _ptr(en[s:]), _ptr(e[s:]),
+                      _stream())
+    return en, e

@@ -1,0 +1,104 @@
+"""Drop-in for the hot-path functions of the reference's ``src/utils.py``.
+
+Same names, parameters, return shapes and Python types; the per-pair set arithmetic runs
+in the sm_100a list-metric kernel (``ops.list_metrics``).  Intersection and union sizes come
+back as exact integers and the ratio is taken in float64 on the host with the reference's own
+expression, so results are bit-identical to the reference's.
+"""
+from __future__ import annotations
+
+from typing import Dict, Hashable, List, Optional, Sequence, Tuple
+
+import numpy as np
+import torch
+
+from . import encode, ops
+
+_ATTRS = ("gender", "age", "occupation")
+
+
+def _device() -> torch.device:
+    if not torch.cuda.is_available():
+        raise RuntimeError("fairness_llm_replication_b200 needs a CUDA device (sm_100a); "
+                           "there is no CPU implementation of the scoring path")
+    return torch.device("cuda", torch.cuda.current_device())
+
+
+def pair_set_counts(lists_a: Sequence[Sequence[Hashable]], lists_b: Sequence[Sequence[Hashable]],
+                    k_cap: Optional[int] = None) -> Tuple[np.ndarray, np.ndarray]:
+    """|set(a[:k]) & set(b[:k])| and |set(a[:k]) | set(b[:k])| for aligned list pairs, on the GPU.
+    Returns two int64 numpy arrays."""
+    P = len(lists_a)
+    if P == 0:
+        return np.zeros(0, np.int64), np.zeros(0, np.int64)
+    a, la, b, lb, vocab = encode.encode_pair_lists(lists_a, lists_b)
+    dev = _device()
+    K = a.shape[1]
+    ta = torch.from_numpy(a).to(dev)
+    tla = torch.from_numpy(la).to(dev)
+    tb = torch.from_numpy(b).to(dev).view(P, 1, K)
+    tlb = torch.from_numpy(lb).to(dev).view(P, 1)
+    res = ops.list_metrics(ta, tla, tb, tlb, vocab=vocab, k_cap=K if k_cap is None else min(int(k_cap), K),
+                           rank_metrics=False, want_union=True, want_sums=False)
+    inter = res.inter.view(P).cpu().numpy().astype(np.int64)
+    union = res.union.view(P).cpu().numpy().astype(np.int64)
+    return inter, union
+
+
+def jaccard_from_counts(inter: np.ndarray, union: np.ndarray, both_empty: float) -> List[float]:
+    """``intersection / union if union > 0`` (src/utils.py:237) in float64; union == 0 means
+    both sets were empty."""
+    safe = np.where(union > 0, union, 1)
+    sims = np.where(union > 0, inter / safe, both_empty)
+    return sims.tolist()
+
+
+def calculate_individual_fairness(profile_pairs: List[Tuple[str, str]],
+                                  recommendations: Dict[str, List[str]]) -> Tuple[float, List[float]]:
+    """Mean pairwise Jaccard similarity -- reference: src/utils.py:217-244.
+
+    Pairs with a pid missing from ``recommendations`` are skipped (:225-226); two empty lists
+    score 1.0 (:232-233); no scored pair gives 0.0 (:242).
+    """
+    kept = [(p, q) for p, q in profile_pairs if p in recommendations and q in recommendations]
+    inter, union = pair_set_counts([recommendations[p] for p, _ in kept],
+                                   [recommendations[q] for _, q in kept])
+    similarity_scores = jaccard_from_counts(inter, union, 1.0)
+    fairness_score = np.mean(similarity_scores) if similarity_scores else 0.0
+    return fairness_score, similarity_scores
+
+
+def create_profile_pairs(profiles: List[Dict], differing_attribute: Optional[str] = None) -> List[Tuple[str, str]]:
+    """Pairs (i < j) of profiles that differ in exactly one of gender / age / occupation among the
+    attributes present in both -- reference: src/utils.py:327-347, same pair order.
+
+    Host logic (it decides which pairs are scored, it scores nothing).  The reference's
+    double Python loop is replaced by blocked integer comparisons, so 10^5 profiles are usable.
+    """
+    n = len(profiles)
+    if n < 2:
+        return []
+    codes = np.zeros((len(_ATTRS), n), np.int64)
+    for a, attr in enumerate(_ATTRS):
+        table: Dict[Hashable, int] = {}
+        for i, p in enumerate(profiles):
+            if attr in p:
+                codes[a, i] = table.setdefault(p[attr], len(table) + 1)
+            # 0 = attribute absent
+    want = None if differing_attribute is None else (
+        _ATTRS.index(differing_attribute) if differing_attribute in _ATTRS else -1)
+    ids = [p["id"] for p in profiles]
+    pairs: List[Tuple[str, str]] = []
+    block = max(1, min(n, (1 << 24) // n))
+    for s in range(0, n, block):
+        e = min(n, s + block)
+        ci = codes[:, s:e, None]
+        cj = codes[:, None, :]
+        differs = (ci != cj) & (ci != 0) & (cj != 0)               # [attr, i, j]
+        ok = differs.sum(axis=0) == 1
+        if want is not None:
+            ok &= differs[want] if want >= 0 else False
+        ok &= np.arange(n)[None, :] > np.arange(s, e)[:, None]     # j > i
+        ii, jj = np.nonzero(ok)
+        pairs.extend((ids[s + i], ids[j]) for i, j in zip(ii.tolist(), jj.tolist()))
+    return pairs

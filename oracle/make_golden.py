@@ -1,0 +1,191 @@
+"""Generate tests/golden/reference_golden.json by running the UNMODIFIED reference
+functions from /root/reference/src on seeded inputs.  Run in the build container:
+
+    python -m oracle.make_golden
+
+TEST INFRASTRUCTURE ONLY.  The JSON holds inputs and the reference's outputs; floats
+round-trip exactly through ``repr``.  The reference has no tests of its own
+(SURVEY.md section 4), so these vectors are what pins the oracle and the CUDA path.
+"""
+from __future__ import annotations
+
+import json
+import os
+import random
+
+import numpy as np
+import pandas as pd
+
+from . import ref_loader
+
+OUT = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))),
+                   "tests", "golden", "reference_golden.json")
+
+TITLES = ["Toy Story", "Heat", "Casino", "Se7en", "Babe", "Clueless", "Fargo", "Twister",
+          "Scream", "Alien", "Aliens", "Psycho", "Jaws", "Rocky", "Gandhi", "Platoon",
+          "Brazil", "Big", "Ghost", "Speed", "Rudy", "Nell", "Congo", "Kids", "Crumb",
+          "Friday", "Nixon", "Sabrina", "Jumanji", "GoldenEye", " Heat", "heat"]
+
+
+def _rand_list(rng, kmax, p_empty=0.1, p_dup=0.2):
+    if rng.random() < p_empty:
+        return []
+    k = rng.randint(1, kmax)
+    lst = [rng.choice(TITLES) for _ in range(k)] if rng.random() < p_dup else rng.sample(TITLES, k)
+    return lst
+
+
+def _profiles(genders, ages, occs, repeats):
+    out = []
+    for g in genders:
+        for a in ages:
+            for o in occs:
+                for r in range(repeats):
+                    out.append({"id": f"p_{g}_{a}_{o}_{r}", "gender": g, "age": a, "occupation": o})
+    return out
+
+
+def main():
+    rng = random.Random(20251203)
+    nrng = np.random.default_rng(20251203)
+    utils = ref_loader.load("utils")
+    p1 = ref_loader.load("phase1_bias_detection")
+    p3 = ref_loader.load("phase3_facter_mitigation")
+    fin = ref_loader.load_script_functions("phase3_final.py")
+    g = {"generator": "oracle/make_golden.py", "reference": "/root/reference/src (unmodified)",
+         "numpy": np.__version__, "pandas": pd.__version__}
+
+    # ---- a1: calculate_individual_fairness (src/utils.py:217) ----
+    cases = []
+    x, y, z, w = "x", "y", "z", "w"
+    fixed = ([("a", "b"), ("c", "d"), ("a", "c"), ("a", "e"), ("a", "zz")],
+             {"a": [x, y, z], "b": [y, z, w], "c": [], "d": [], "e": [x, x, y]})
+    inputs = [fixed, ([], {}), ([("a", "b")], {"a": [], "b": []})]
+    for _ in range(12):
+        pids = [f"u{i}" for i in range(rng.randint(2, 14))]
+        recs = {p: _rand_list(rng, 20) for p in pids if rng.random() > 0.1}
+        pairs = [(rng.choice(pids), rng.choice(pids)) for _ in range(rng.randint(1, 40))]
+        inputs.append((pairs, recs))
+    for pairs, recs in inputs:
+        score, sims = utils.calculate_individual_fairness(pairs, recs)
+        cases.append({"pairs": [list(p) for p in pairs], "recs": recs,
+                      "score": float(score), "sims": [float(s) for s in sims]})
+    g["individual_fairness"] = cases
+
+    # ---- a3: create_profile_pairs (src/utils.py:327) ----
+    cases = []
+    prof45 = _profiles(["male", "female", "non-binary"], ["18-24", "25-34", "35-44", "45-54", "55+"],
+                       ["professional"], 3)
+    sets = [prof45, _profiles(["m", "f"], ["a", "b"], ["x", "y", "z"], 1)]
+    odd = _profiles(["m", "f"], ["a", "b"], ["x"], 2)
+    del odd[3]["age"]
+    del odd[5]["occupation"]
+    sets.append(odd)
+    for profs in sets:
+        for attr in (None, "gender", "age", "occupation"):
+            pairs = utils.create_profile_pairs(profs, attr)
+            cases.append({"profiles": profs, "attr": attr, "pairs": [list(p) for p in pairs]})
+    g["profile_pairs"] = cases
+
+    # ---- a2: measure_individual_fairness (src/phase1_bias_detection.py:220) ----
+    cases = []
+    for _ in range(3):
+        recs = {p["id"]: {"profile_id": p["id"], "recommendations": _rand_list(rng, 10)}
+                for p in prof45 if rng.random() > 0.05}
+        if recs:
+            first = next(iter(recs))
+            recs[first] = {"profile_id": first, "error": "boom"}      # row without 'recommendations'
+        score, det = p1.measure_individual_fairness(prof45, recs)
+        cases.append({"profiles": prof45, "recs": recs, "score": float(score),
+                      "sims": [float(s) for s in det["similarity_scores"]],
+                      "num_pairs": int(det["num_pairs"]), "std": float(det["std_similarity"])})
+    g["measure_individual_fairness"] = cases
+
+    # ---- a4: measure_quality_preservation (src/phase3_facter_mitigation.py:333) ----
+    cases = []
+    letters = list("abcdefghijklmnop")
+    inputs = [({"u": letters[:12]}, {"u": ["a", "b", "c", "x", "y", "z"]}), ({}, {}),
+              ({"u": []}, {"u": []}), ({"u": ["a"]}, {"v": ["a"]})]
+    for _ in range(6):
+        pids = [f"u{i}" for i in range(rng.randint(1, 12))]
+        o = {p: (_rand_list(rng, 16) if rng.random() < 0.5 else {"recommendations": _rand_list(rng, 16)})
+             for p in pids}
+        m = {p: (_rand_list(rng, 16) if rng.random() < 0.5 else {"recommendations": _rand_list(rng, 16)})
+             for p in pids if rng.random() > 0.15}
+        inputs.append((o, m))
+    for o, m in inputs:
+        r = p3.measure_quality_preservation(o, m)
+        cases.append({"orig": o, "mitg": m, "average_overlap": float(r["average_overlap"]),
+                      "quality_preservation_pct": float(r["quality_preservation_pct"]),
+                      "num_comparisons": int(r["num_comparisons"])})
+    g["quality_preservation"] = cases
+
+    # ---- a5: phase3_final.jaccard / measure_fairness (src/phase3_final.py:112,119) ----
+    cases = []
+    for s1, s2 in [([], []), (["a"], []), (["a", "b"], ["b", "c"]), (["a"], ["a"])]:
+        cases.append({"s1": s1, "s2": s2, "jaccard": float(fin.jaccard(set(s1), set(s2)))})
+    g["final_jaccard"] = cases
+    cases = []
+    inputs = [{"g1": [["a"]]}, {"g1": [[]], "g2": [[]]}, {"g1": [], "g2": []}]
+    for _ in range(8):
+        n1, n2 = rng.randint(1, 8), rng.randint(1, 8)
+        d = {"male": [_rand_list(rng, 10) for _ in range(n1)],
+             "female": [_rand_list(rng, 10) for _ in range(n2)]}
+        if rng.random() < 0.4:
+            d["non-binary"] = [_rand_list(rng, 10)]
+        inputs.append(d)
+    for d in inputs:
+        cases.append({"recs_by_group": d, "fairness": float(fin.measure_fairness(d))})
+    g["measure_fairness"] = cases
+
+    # ---- a9: calculate_conformal_thresholds (src/phase3_facter_mitigation.py:152) ----
+    cases = []
+    fixed = pd.DataFrame({"group": ["m"] * 10 + ["f"] * 3,
+                          "nonconformity": [.05, .01, .09, .03, .07, .02, .10, .04, .08, .06, .5, .2, .9]})
+    frames = [(fixed, 0.1)]
+    for _ in range(8):
+        n = rng.randint(1, 400)
+        groups = nrng.choice(["male", "female", "non-binary"], size=n)
+        sc = np.abs(nrng.normal(0, 0.1, size=n))
+        if rng.random() < 0.5:
+            sc = np.round(sc, 2)                      # heavy ties
+        frames.append((pd.DataFrame({"group": groups, "nonconformity": sc}),
+                       rng.choice([0.1, 0.05, 0.2, 0.5, 0.01])))
+    for df, alpha in frames:
+        thr = p3.calculate_conformal_thresholds(df, alpha)
+        cases.append({"group": list(df["group"]), "nonconformity": [float(v) for v in df["nonconformity"]],
+                      "alpha": alpha, "thresholds": {k: float(v) for k, v in thr.items()}})
+    g["conformal_thresholds"] = cases
+    g["conformal_index"] = [{"n": n, "alpha": a, "index": max(0, min(int(np.ceil((n + 1) * (1 - a))) - 1, n - 1))}
+                            for n in (1, 2, 3, 9, 10, 11, 19, 20, 99, 100, 1000, 187240, 1000000, 310000000)
+                            for a in (0.1, 0.05, 0.2)]
+
+    # ---- a10: apply_conformal_filtering (src/phase3_facter_mitigation.py:184) ----
+    cases = []
+    profs = [{"id": f"u{i}", "gender": ["male", "female", "other"][i % 3]} for i in range(9)]
+    for thr in ({"male": 0.8, "female": 0.95}, {"male": 0.0, "female": 1.0, "other": 0.55},
+                {"male": 0.5000000001, "female": 0.85, "other": 0.15}):
+        recs = {f"u{i}": {"recommendations": [f"m{j}" for j in range(rng.randint(0, 22))]} for i in range(9)}
+        recs["ghost"] = {"recommendations": ["a", "b", "c"]}
+        recs["u2"] = {}
+        out = p3.apply_conformal_filtering(recs, profs, thr)
+        cases.append({"recs": recs, "profiles": profs, "thresholds": thr, "filtered": out})
+    g["conformal_filtering"] = cases
+
+    # ---- a8: generate_calibration_data (src/phase3_facter_mitigation.py:109), seeded ----
+    profs = [{"id": f"u{i}", "gender": ["male", "female"][i % 2]} for i in range(6)]
+    recs = {f"u{i}": {"recommendations": [f"m{j}" for j in range(i + 1)]} for i in range(5)}
+    recs["u3"] = {"error": "x"}
+    np.random.seed(1234)
+    df = p3.generate_calibration_data(profs, recs, {"m0": 0.75})
+    g["calibration_data"] = {"profiles": profs, "recs": recs, "ratings": {"m0": 0.75}, "seed": 1234,
+                             "columns": {c: [v if isinstance(v, str) else float(v) for v in df[c]]
+                                         for c in df.columns}}
+
+    with open(OUT, "w") as f:
+        json.dump(g, f, indent=0, sort_keys=True)
+    print("wrote", OUT, os.path.getsize(OUT), "bytes")
+
+
+if __name__ == "__main__":
+    main()
