@@ -1,0 +1,293 @@
+#!/usr/bin/env python
+"""Benchmark of the scoring hot path (BASELINE.json: user-variant pairs/s, list metrics +
+conformal scoring).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+
+A step is one pass of the full pipeline (list metrics -> cosine nonconformity -> exact global
+quantile -> threshold schedule -> violation flags) over one shard of synthetic users of the
+10M-user sweep (BASELINE.json configs[4]; configs[1] is 15 MB and launch-bound, SURVEY.md
+section 7): 1.25M users x 31 variants per GPU, top-50 lists, 384-d fp32 embeddings, i.e.
+exactly the 10M-user job at 8 GPUs and its per-GPU shard below that (weak scaling).
+
+Prints ONE JSON line (rank 0).  `value` is device-resident throughput, `e2e` is the same
+pipeline called with pinned HOST buffers (H2D and the D2H of the summary inside the timing).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "user_variant_pairs_per_sec"
+UNIT = "pairs/s"
+FALLBACK_HBM_GBS = 6650.0          # /opt/skills/guides/B200_PROFILING.md fallback
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--users-per-gpu", type=int, default=1_250_000)
+    ap.add_argument("--e2e-users", type=int, default=65_536)
+    ap.add_argument("--cpu-sample-users", type=int, default=4096)
+    ap.add_argument("--list-len", type=int, default=50)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+def workload_config(args, n_gpus):
+    return {
+        "workload": "cfg5-shard: 10M-user sweep sharded by users (1.25M users/GPU at the default), "
+                    "31 variants, top-%d lists over 3706 items, 384-d fp32 embeddings, full pipeline" % args.list_len,
+        "users_per_gpu": args.users_per_gpu, "n_variants": 31, "list_len": args.list_len, "emb_dim": 384,
+        "vocab": 3706, "alpha": 0.1, "gamma": 0.95, "rounds": 4,
+        "parallelism": "user-sharded dp%d" % n_gpus,
+        "l2": "inputs (%.1f GB per GPU) are larger than the 126 MB L2; no flush needed"
+              % (args.users_per_gpu * (32 * args.list_len * 4 + 32 * 4 + 32 * 384 * 4) / 1e9),
+    }
+
+
+# ---------------------------------------------------------------------------------- clocks
+class ClockSampler:
+    """Samples SM clock + throttle reasons through NVML while the timed region runs."""
+    REASONS = {0x4: "sw_power_cap", 0x8: "hw_slowdown", 0x20: "sw_thermal_slowdown",
+               0x40: "hw_thermal_slowdown", 0x80: "hw_power_brake_slowdown", 0x2: "applications_clocks_setting"}
+
+    def __init__(self, index):
+        self.samples, self.reasons, self.max_mhz, self._stop = [], set(), None, threading.Event()
+        self.ok = False
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = int(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
+            self.ok = True
+        except Exception:
+            self.ok = False
+        self.thread = threading.Thread(target=self._loop, daemon=True)
+
+    def _loop(self):
+        while not self._stop.is_set():
+            try:
+                self.samples.append(int(self.nv.nvmlDeviceGetClockInfo(self.h, self.nv.NVML_CLOCK_SM)))
+                mask = int(self.nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h))
+                for bit, name in self.REASONS.items():
+                    if mask & bit:
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            time.sleep(0.01)
+
+    def start(self):
+        if self.ok:
+            self.thread.start()
+
+    def stop(self):
+        self._stop.set()
+        if self.ok:
+            self.thread.join(timeout=2)
+        return {"sm_mhz": float(np.median(self.samples)) if self.samples else None, "sm_max_mhz": self.max_mhz,
+                "reasons": sorted(self.reasons), "samples": len(self.samples)}
+
+
+def hbm_peak():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    try:
+        return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return FALLBACK_HBM_GBS, "fallback (B200_PROFILING.md)"
+
+
+def ncu_traffic(kernel):
+    """Per-launch DRAM bytes of `kernel` from the committed ncu capture, if one has been summarised."""
+    try:
+        d = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
+        return d.get(kernel)
+    except Exception:
+        return None
+
+
+# ---------------------------------------------------------------------------------- CPU arm
+def cpu_sample(args, n_users, user0=0):
+    """Time the oracle pipeline (oracle/cpu_pipeline.py) on a bounded sample, all host cores."""
+    from fairness_llm_replication_b200 import ops
+    from oracle import cpu_pipeline
+    V, K, D = 31, args.list_len, 384
+    lists = ops.synth_lists_host(20251203, user0, n_users, V, K, 3706)        # host generator, no GPU
+    embs = ops.synth_embeddings_host(20251203, user0, n_users, V, D)
+    cores = os.cpu_count() or 1
+    _, dt = cpu_pipeline.run((*lists, *embs), workers=cores)
+    return n_users * V / dt, dt, cores
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    cfg = workload_config(args, args.gpus)
+    steps, warm = max(1, args.steps), max(0, args.warmup)
+    # bounded: about 1-2 s of CPU work per step
+    n = args.cpu_sample_users
+    for _ in range(min(warm, 1)):
+        cpu_sample(args, min(n, 512))
+    times, pairs, cores = [], 0, 1
+    for s in range(steps):
+        v, dt, cores = cpu_sample(args, n, user0=s * n)
+        times.append(dt)
+        pairs += n * 31
+    value = pairs / sum(times)
+    sample = "%d users x 31 variants per step (full pipeline: list metrics + cosine + quantile + violations)" % n
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": steps,
+        "warmup": warm, "ms_per_step": 1e3 * sum(times) / steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": cfg,
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+        "note": "numpy oracle port on host cores; the reference tree is Python-only, has no code for "
+                "SERP*/PRAG*/cosine/violations and cannot travel to the GPU box",
+    }
+    print(json.dumps(line))
+
+
+# ---------------------------------------------------------------------------------- our arm
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    from fairness_llm_replication_b200 import ops, pipeline
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the scoring path has no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    distributed = world > 1
+    if distributed:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+    n_gpus = world
+
+    def barrier():
+        if distributed:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x):
+        if not distributed:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    cfg = pipeline.PipelineConfig(list_len=args.list_len)
+    V, K, D = cfg.n_variants, cfg.list_len, cfg.emb_dim
+    U = args.users_per_gpu
+    batch = pipeline.synth_batch(cfg, rank * U, U, dev)
+    torch.cuda.synchronize()
+    pipe = pipeline.ScoringPipeline(cfg, distributed=distributed)
+    steps, warm = max(1, args.steps), max(3, args.warmup)
+
+    for _ in range(warm):
+        res = pipe.run(batch)
+    barrier()
+    sampler = ClockSampler(local)
+    sampler.start()
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+    pipe.kernel_events = []
+    launches0 = pipe.n_launches
+    barrier()
+    ev[0].record()
+    for _ in range(steps):
+        res = pipe.run(batch)
+    ev[1].record()
+    barrier()
+    clocks = sampler.stop()
+    ms_total = max_over_ranks(ev[0].elapsed_time(ev[1]))
+    launches = pipe.n_launches - launches0
+    kernel_ms = {}
+    for name, a, b in pipe.kernel_events:
+        kernel_ms.setdefault(name, []).append(a.elapsed_time(b))
+    pipe.kernel_events = None
+    summary = pipe.summarize(res)
+    pairs_per_step = U * V * n_gpus
+    value = pairs_per_step * steps / (ms_total * 1e-3)
+
+    # ---- end to end: pinned host buffers in, summary out ----
+    e2e = None
+    if not args.no_e2e:
+        E = min(args.e2e_users, U)
+        hb = pipeline.synth_batch_host(cfg, rank * U, E, pin=True)
+        for _ in range(2):
+            pipe.run_host(hb, dev)
+        barrier()
+        t0 = time.perf_counter()
+        e2e_steps = max(3, min(steps, 10))
+        for _ in range(e2e_steps):
+            _, summ = pipe.run_host(hb, dev)
+        barrier()
+        dt = max_over_ranks(time.perf_counter() - t0)
+        d2h = res.reduced.numel() * 8 + res.thresholds.numel() * 4 + res.select_state.numel() * 8 + 4
+        e2e = {"value": E * V * n_gpus * e2e_steps / dt, "unit": UNIT, "h2d_bytes_per_step": hb.nbytes(),
+               "d2h_bytes_per_step": d2h, "users_per_gpu_per_step": E, "steps": e2e_steps,
+               "note": "ScoringPipeline.run_host: chunked H2D from pinned memory overlapped with the kernels"}
+        del hb
+
+    if rank == 0:
+        peak, peak_src = hbm_peak()
+        pairs_gpu = U * V
+        roof = {}
+        for name, bytes_per_pair in (("cosine_kernel", D * 4 * (V + 1) / V + 4),
+                                     ("list_metrics_table_kernel", K * 4 * (V + 1) / V + 4 * (V + 1) / V + 16)):
+            if kernel_ms.get(name):
+                t = float(np.mean(kernel_ms[name])) * 1e-3
+                ach = pairs_gpu * bytes_per_pair / t / 1e9
+                roof[name] = {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
+                              "traffic": ncu_traffic(name), "kernel": name, "avg_launch_ms": t * 1e3,
+                              "algorithmic_bytes_per_launch": pairs_gpu * bytes_per_pair,
+                              "peak_source": peak_src, "frac_of_nominal_8000": ach / 8000.0}
+        cpu = None
+        if n_gpus == 1 and not args.no_cpu_baseline:
+            v, dt, cores = cpu_sample(args, args.cpu_sample_users)
+            cpu = {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
+                   "sample": "%d users x 31 variants, full pipeline, %.1f s" % (args.cpu_sample_users, dt)}
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": n_gpus, "steps": steps, "warmup": warm,
+            "ms_per_step": ms_total / steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic", "config": workload_config(args, n_gpus), "e2e": e2e,
+            "gpu_launches": launches, "clocks": clocks,
+            "roofline": roof.get("cosine_kernel"), "roofline_list_metrics": roof.get("list_metrics_table_kernel"),
+            "cpu_baseline": cpu,
+            "step_kernel_ms": {k: float(np.mean(v)) for k, v in kernel_ms.items()},
+            "check": {"threshold": float(summary["thresholds"][0]), "violations_round0": int(summary["violation_counts"][0]),
+                      "mean_jaccard_v0": float(summary["variant_means"][0, 0])},
+        }
+        print(json.dumps(line))
+    if distributed:
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -111,6 +111,17 @@ class ScoringPipeline:
         self.distributed = distributed
         self.pg = process_group
         self.n_launches = 0          # kernels of this library enqueued so far
+        self.kernel_events = None    # bench.py sets a list to collect (name, start, end) CUDA events
+
+    def _timed(self, name, fn):
+        if self.kernel_events is None:
+            return fn()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        out = fn()
+        b.record()
+        self.kernel_events.append((name, a, b))
+        return out
 
     # -- collectives -------------------------------------------------------------------
     def _all_reduce(self, t: torch.Tensor) -> None:
@@ -124,9 +135,10 @@ class ScoringPipeline:
         V, R = cfg.n_variants, cfg.rounds
         dev = b.lists.device
         hist0 = torch.zeros(ops.SELECT_BINS, dtype=torch.int64, device=dev)
-        lm = ops.list_metrics(b.neutral, b.neutral_len, b.lists, b.lens, vocab=cfg.vocab, k_cap=cfg.k_cap,
-                              empty_policy=cfg.empty_policy, rank_metrics=True, want_union=False, want_sums=True)
-        scores = ops.cosine_nonconformity(b.emb_neutral, b.emb, hist0=hist0)
+        lm = self._timed("list_metrics_table_kernel", lambda: ops.list_metrics(
+            b.neutral, b.neutral_len, b.lists, b.lens, vocab=cfg.vocab, k_cap=cfg.k_cap,
+            empty_policy=cfg.empty_policy, rank_metrics=True, want_union=False, want_sums=True))
+        scores = self._timed("cosine_kernel", lambda: ops.cosine_nonconformity(b.emb_neutral, b.emb, hist0=hist0))
         self.n_launches += 3
         return self._finish(lm.inter, lm.jaccard, lm.serp, lm.prag, lm.variant_sums, lm.status, scores, hist0)
 

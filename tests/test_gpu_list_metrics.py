@@ -1,0 +1,227 @@
+"""GPU parity of the list-metric kernels (through the C ABI) against the CPU oracle and the
+reference's golden vectors.  Integer outputs bit-exact; float ratios within 1e-6 relative."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import np_oracle as O
+
+pytestmark = pytest.mark.gpu
+RTOL = 1e-6          # north_star: rank metrics within 1e-6 relative
+
+
+def _run(neutral, nlen, lists, lens, **kw):
+    from fairness_llm_replication_b200 import ops
+    dev = torch.device("cuda", 0)
+    t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
+    res = ops.list_metrics(t(neutral), t(nlen), t(lists), t(lens), want_union=True, **kw)
+    torch.cuda.synchronize()
+    return res
+
+
+def _check(neutral, nlen, lists, lens, vocab, k_cap=None, empty_policy=1, rank=True):
+    res = _run(neutral, nlen, lists, lens, vocab=vocab, k_cap=k_cap, empty_policy=empty_policy, rank_metrics=rank)
+    want = O.list_metrics(neutral, nlen, lists, lens, k_cap=k_cap, empty_policy=empty_policy)
+    assert np.array_equal(res.inter.cpu().numpy(), want["inter"])
+    assert np.array_equal(res.union.cpu().numpy(), want["union"])
+    np.testing.assert_allclose(res.jaccard.cpu().numpy(), want["jaccard"], rtol=RTOL, atol=0)
+    sums = res.variant_sums.cpu().numpy()
+    np.testing.assert_allclose(sums[:, 0], want["jaccard"].sum(0), rtol=1e-12)
+    assert np.array_equal(sums[:, 3], np.full(lists.shape[1], lists.shape[0]))
+    if rank:
+        np.testing.assert_allclose(res.serp.cpu().numpy(), want["serp"], rtol=RTOL, atol=0)
+        np.testing.assert_allclose(res.prag.cpu().numpy(), want["prag"], rtol=RTOL, atol=0)
+        assert np.array_equal(sums[:, 1], want["serp_num"].sum(0))          # integer sums: exact
+        assert np.array_equal(sums[:, 2], want["prag_num"].sum(0))
+        means = res.variant_means().cpu().numpy()
+        np.testing.assert_allclose(means[:, 1], want["serp"].mean(0), rtol=1e-12)
+    assert int(res.status.item()) == 0
+    return res, want
+
+
+def _random_case(rng, U, V, K, vocab, p_dup=0.3):
+    neutral = rng.integers(0, vocab, size=(U, K)).astype(np.int32)
+    lists = np.where(rng.random((U, V, K)) < 0.5, neutral[:, None, :], rng.integers(0, vocab, size=(U, V, K)))
+    lists = lists.astype(np.int32)
+    shuffle = rng.random((U, V)) < 0.5
+    perm = rng.permuted(np.broadcast_to(np.arange(K), (U, V, K)), axis=-1)
+    lists = np.where(shuffle[..., None], np.take_along_axis(lists, perm, -1), lists)
+    nlen = np.where(rng.random(U) < 0.2, rng.integers(0, K + 1, U), K).astype(np.int32)
+    lens = np.where(rng.random((U, V)) < 0.2, rng.integers(0, K + 1, (U, V)), K).astype(np.int32)
+    if p_dup == 0:
+        pass
+    return neutral, nlen, lists, lens
+
+
+@pytest.mark.parametrize("V,K", [(31, 20), (31, 50), (31, 64), (32, 10), (7, 13), (16, 3), (2, 1), (64, 8)])
+def test_table_kernel_random(V, K):
+    rng = np.random.default_rng(V * 100 + K)
+    vocab = 3706 if K > 8 else 40            # small vocab => many duplicates and hits
+    case = _random_case(rng, 203, V, K, vocab)
+    _check(*case, vocab=vocab)
+    _check(*case, vocab=vocab, empty_policy=0)
+    _check(*case, vocab=vocab, rank=False)
+    if K > 4:
+        _check(*case, vocab=vocab, k_cap=K // 2)
+
+
+@pytest.mark.parametrize("V,K,vocab", [(1, 10, 500), (1, 20, 100000), (3, 64, 50), (124, 20, 3706), (5, 12, 70000)])
+def test_compare_kernel_shapes(V, K, vocab):
+    """V = 1 pair lists (string API), huge vocabularies and V > 128 go through the compare kernel."""
+    rng = np.random.default_rng(K)
+    case = _random_case(rng, 150, V, K, min(vocab, 60))
+    _check(*case, vocab=vocab)
+    _check(*case, vocab=vocab, empty_policy=0, k_cap=max(1, K - 3))
+
+
+def test_jaccard_only_long_lists():
+    rng = np.random.default_rng(9)
+    case = _random_case(rng, 40, 2, 200, 300)
+    _check(*case, vocab=300, rank=False)
+    from fairness_llm_replication_b200 import _lib
+    with pytest.raises(_lib.FlrError):
+        _run(*case, vocab=300, rank_metrics=True)            # SERP/PRAG need k_cap <= 64
+
+
+def test_heavy_duplicates_and_empties():
+    rng = np.random.default_rng(1)
+    U, V, K = 97, 31, 20
+    neutral = rng.integers(0, 6, size=(U, K)).astype(np.int32)        # 6 distinct ids in 20 slots
+    lists = rng.integers(0, 8, size=(U, V, K)).astype(np.int32)
+    nlen = rng.integers(0, 3, U).astype(np.int32) * 10
+    lens = rng.integers(0, 3, (U, V)).astype(np.int32) * 10
+    for pol in (0, 1):
+        _check(neutral, nlen, lists, lens, vocab=3706, empty_policy=pol)
+
+
+def test_padding_is_never_read_as_ids():
+    rng = np.random.default_rng(4)
+    neutral, nlen, lists, lens = _random_case(rng, 64, 31, 20, 3706)
+    pos = np.arange(20)
+    g_neutral = np.where(pos[None] < nlen[:, None], neutral, -1).astype(np.int32)
+    g_lists = np.where(pos[None, None] < lens[..., None], lists, 2 ** 31 - 1).astype(np.int32)
+    a, _ = _check(neutral, nlen, lists, lens, vocab=3706)
+    b, _ = _check(g_neutral, nlen, g_lists, lens, vocab=3706)
+    assert torch.equal(a.inter, b.inter) and torch.equal(a.prag, b.prag)
+
+
+def test_out_of_vocab_ids_are_counted_and_skipped():
+    neutral = np.array([[1, 2, 3, 4]], np.int32)
+    lists = np.array([[[1, 99, 2, -5]], [[0, 0, 0, 0]]], np.int32).reshape(1, 2, 4)
+    res = _run(neutral, np.array([4], np.int32), lists, np.array([[4, 1]], np.int32), vocab=10)
+    assert res.inter.cpu().tolist() == [[2, 0]] and int(res.status.item()) == 2
+    assert res.union.cpu().tolist() == [[4, 5]]
+
+
+def test_tail_tiles_and_tiny_inputs():
+    rng = np.random.default_rng(12)
+    for U in (1, 2, 3, 4, 5, 7, 9, 301):
+        _check(*_random_case(rng, U, 31, 20, 3706), vocab=3706)
+
+
+def test_unaligned_views_take_the_plain_load_path():
+    rng = np.random.default_rng(13)
+    from fairness_llm_replication_b200 import ops
+    neutral, nlen, lists, lens = _random_case(rng, 41, 31, 10, 3706)
+    dev = torch.device("cuda", 0)
+    def off(a):                      # same data at a 4-byte offset: not 16-byte aligned
+        flat = torch.empty(a.size + 1, dtype=torch.int32, device=dev)
+        flat[1:] = torch.from_numpy(a.ravel()).to(dev)
+        return flat[1:].view(a.shape)
+    res = ops.list_metrics(off(neutral), off(nlen), off(lists), off(lens), vocab=3706, want_union=True)
+    want = O.list_metrics(neutral, nlen, lists, lens)
+    assert np.array_equal(res.inter.cpu().numpy(), want["inter"])
+    np.testing.assert_allclose(res.prag.cpu().numpy(), want["prag"], rtol=RTOL)
+
+
+def test_synthetic_config2_full_size_matches_oracle():
+    """BASELINE.json configs[1]: 6040 users x 31 variants, K=20 -- small enough for the oracle."""
+    from fairness_llm_replication_b200 import ops
+    U, V, K, vocab = 6040, 31, 20, 3706
+    host = ops.synth_lists_host(20251203, 0, U, V, K, vocab)
+    devt = ops.synth_lists(20251203, 0, U, V, K, vocab, "cuda:0")
+    for h, d in zip(host, devt):
+        assert np.array_equal(h, d.cpu().numpy())                  # device generator == host generator
+    res, want = _check(*host, vocab=vocab)
+    spreads = O.snsr_snsv(want["jaccard"].mean(0))
+    got = O.snsr_snsv(res.variant_means().cpu().numpy()[:, 0])
+    for a in spreads:
+        assert got[a]["snsr"] == pytest.approx(spreads[a]["snsr"], rel=1e-9)
+        assert got[a]["snsv"] == pytest.approx(spreads[a]["snsv"], rel=1e-9)
+
+
+def test_large_k50_properties():
+    """Config-5 shape (K=50) at a size the oracle cannot sweep: size-independent properties."""
+    from fairness_llm_replication_b200 import ops
+    U, V, K, vocab = 200_000, 31, 50, 3706
+    neutral, nlen, lists, lens = ops.synth_lists(20251203, 0, U, V, K, vocab, "cuda:0")
+    res = ops.list_metrics(neutral, nlen, lists, lens, vocab=vocab, want_union=True)
+    # (1) a slice must equal the oracle
+    sl = slice(123_400, 123_700)
+    want = O.list_metrics(neutral[sl].cpu().numpy(), nlen[sl].cpu().numpy(), lists[sl].cpu().numpy(),
+                          lens[sl].cpu().numpy())
+    assert np.array_equal(res.inter[sl].cpu().numpy(), want["inter"])
+    np.testing.assert_allclose(res.prag[sl].cpu().numpy(), want["prag"], rtol=RTOL)
+    # (2) every list against itself: Jaccard 1, SERP/PRAG closed forms of the distinct prefix
+    same = ops.list_metrics(neutral, nlen, neutral.view(U, 1, K).expand(U, V, K).contiguous(),
+                            nlen.view(U, 1).expand(U, V).contiguous(), vocab=vocab, want_union=True)
+    assert torch.equal(same.inter, same.union)
+    full = (nlen == K) & (same.inter[:, 0] == K)
+    assert torch.all(same.serp[full] == 1.0)
+    assert torch.allclose(same.prag[full], torch.tensor((K * (K - 1) / 2) / (K * (K + 1))))
+    # (3) sums are the column sums of the per-pair outputs
+    assert torch.equal(res.variant_sums[:, 3], torch.full((V,), float(U), dtype=torch.float64, device="cuda:0"))
+    assert torch.allclose(res.variant_sums[:, 0], res.jaccard.double().sum(0), rtol=1e-6)
+    # (4) 0 <= inter <= min sizes, union consistent
+    assert int(res.inter.min()) >= 0 and torch.all(res.inter <= res.union)
+    # (5) idempotent
+    again = ops.list_metrics(neutral, nlen, lists, lens, vocab=vocab, want_union=True)
+    assert torch.equal(again.inter, res.inter) and torch.equal(again.prag, res.prag)
+    assert torch.equal(again.variant_sums, res.variant_sums)       # fixed-order reduction: bit-reproducible
+
+
+# ---- string API against the reference's golden outputs ------------------------------------------
+def test_dropin_individual_fairness(golden):
+    from fairness_llm_replication_b200 import utils
+    for c in golden["individual_fairness"]:
+        score, sims = utils.calculate_individual_fairness([tuple(p) for p in c["pairs"]], c["recs"])
+        assert sims == c["sims"] and float(score) == c["score"]
+        assert all(type(s) is float for s in sims)
+
+
+def test_dropin_measure_individual_fairness(golden):
+    from fairness_llm_replication_b200 import phase1_bias_detection as p1
+    for c in golden["measure_individual_fairness"]:
+        score, det = p1.measure_individual_fairness(c["profiles"], c["recs"])
+        assert float(score) == c["score"] and det["similarity_scores"] == c["sims"]
+        assert det["num_pairs"] == c["num_pairs"] and float(det["std_similarity"]) == c["std"]
+        assert float(det["mean_similarity"]) == c["score"]
+
+
+def test_dropin_quality_preservation(golden):
+    from fairness_llm_replication_b200 import phase3_facter_mitigation as p3
+    for c in golden["quality_preservation"]:
+        r = p3.measure_quality_preservation(c["orig"], c["mitg"])
+        assert float(r["average_overlap"]) == c["average_overlap"]
+        assert float(r["quality_preservation_pct"]) == c["quality_preservation_pct"]
+        assert r["num_comparisons"] == c["num_comparisons"]
+
+
+def test_dropin_phase3_final(golden):
+    from fairness_llm_replication_b200 import phase3_final as fin
+    for c in golden["final_jaccard"]:
+        assert fin.jaccard(set(c["s1"]), set(c["s2"])) == c["jaccard"]
+    for c in golden["measure_fairness"]:
+        assert float(fin.measure_fairness(c["recs_by_group"])) == c["fairness"]
+
+
+def test_pair_jaccard_bitsets():
+    from fairness_llm_replication_b200 import ops
+    rng = np.random.default_rng(21)
+    for (U, M, K, vocab) in [(5, 124, 20, 3706), (3, 7, 5, 40), (2, 33, 50, 3706)]:
+        lists = rng.integers(0, min(vocab, 200), size=(U, M, K)).astype(np.int32)
+        lens = rng.integers(0, K + 1, size=(U, M)).astype(np.int32)
+        inter, sizes = ops.pair_jaccard(torch.from_numpy(lists).cuda(), torch.from_numpy(lens).cuda(), vocab=vocab)
+        want = O.pair_jaccard(lists, lens)
+        assert np.array_equal(inter.cpu().numpy(), want["inter"])
+        assert np.array_equal(sizes.cpu().numpy(), want["sizes"])
