@@ -13,6 +13,7 @@ LIB_PATH = os.path.join(_PKG, "libflr_b200.so")
 OK, E_INVALID, E_UNSUPPORTED, E_CUDA, E_SCRATCH = 0, -1, -2, -3, -4
 EMPTY_ANY_IS_ZERO, EMPTY_BOTH_IS_ONE = 0, 1
 MAX_RANK_K, SELECT_BINS, MAX_ROUNDS, SELECT_STATE_WORDS = 64, 2048, 8, 8
+LIST_METRICS_STATIC_SCRATCH_BYTES = 2097152
 DTYPE_F32, DTYPE_F64 = 0, 1
 ST_PREFIX, ST_KREM, ST_N, ST_K, ST_LESS, ST_EQUAL, ST_EMPTY = range(7)
 
@@ -34,6 +35,8 @@ SIGNATURES = {
     "flr_list_metrics_scratch_bytes": (_sz, [_i64, _i32, _i32, _i32]),
     "flr_list_metrics": (_i32, [_vp, _vp, _vp, _vp, _i64, _i32, _i32, _i32, _i32, _i32, _i32,
                                 _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),
+    "flr_list_metrics_static": (_i32, [_vp, _vp, _vp, _vp, _i64, _i32, _i32, _i32, _i32, _i32, _i32,
+                                       _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "flr_pair_jaccard": (_i32, [_vp, _vp, _i64, _i32, _i32, _i32, _vp, _vp, _vp]),
     "flr_cosine_nonconformity": (_i32, [_vp, _vp, _i64, _i32, _i32, _vp, _vp, _vp]),
     "flr_select_num_passes": (_i32, [_i32]),

@@ -12,6 +12,7 @@
 // Compare kernel: vocabulary-independent O(K^2) fallback for shapes the table kernel does
 // not cover (V = 1 pair lists of the string API, huge vocabularies, K > 64 Jaccard-only).
 #include <algorithm>
+#include <mutex>
 
 #include "common.cuh"
 
@@ -476,6 +477,125 @@ extern "C" int flr_list_metrics(const int32_t *neutral, const int32_t *neutral_l
             list_metrics_cmp_finalize_kernel<<<(V + 127) / 128, 128, 0, stream>>>(p.partial, pl.cmp_threads, V,
                                                                                    out_variant_sums);
             FLR_LAUNCH_CHECK("list_metrics_cmp_finalize_kernel");
+        }
+    }
+    return FLR_OK;
+}
+
+// ---------------------------------------------------------------------------------------
+// flr_list_metrics_static: the same computation for callers that cannot supply scratch.
+//
+// Who that is: a process whose GPU memory was planned by someone else -- a serving worker
+// whose HBM was handed to one pool up front, a job that sized its user shard to fill the
+// device, a step loop that must never run into cudaMalloc's device-wide synchronisation.
+// Such a caller owns its input and output buffers but has no way to come up with one more
+// buffer for the per-thread partial sums.  Here those partials live in the fixed array
+// below, which is part of the library image: every GPU that loads the library gives up
+// FLR_LIST_METRICS_STATIC_SCRATCH_BYTES for as long as the process lives.
+//
+// In host code `g_lm_static_scratch` is only a handle; the address the kernels need comes
+// from cudaGetSymbolAddress, looked up once per device, with that device current, by the
+// first call made on it.
+// ---------------------------------------------------------------------------------------
+static __device__ __align__(256) unsigned char g_lm_static_scratch[FLR_LIST_METRICS_STATIC_SCRATCH_BYTES];
+
+namespace {
+
+constexpr int kMaxDevices = 64;
+double *g_static_ptr[kMaxDevices];     // device address of g_lm_static_scratch, per device ordinal
+bool g_static_ready[kMaxDevices];
+std::mutex g_static_mutex;
+
+// Runs the one-time lookup for the current device if it has not been done yet.
+int static_scratch_for_current_device(double **out) {
+    int dev = -1;
+    FLR_CUDA(cudaGetDevice(&dev));
+    FLR_REQUIRE(dev >= 0 && dev < kMaxDevices, FLR_E_UNSUPPORTED,
+                "list_metrics_static: device ordinal %d outside [0, %d)", dev, kMaxDevices);
+    std::lock_guard<std::mutex> lock(g_static_mutex);
+    if (!g_static_ready[dev]) {
+        void *ptr = nullptr;
+        FLR_CUDA(cudaGetSymbolAddress(&ptr, g_lm_static_scratch));
+        FLR_REQUIRE(ptr != nullptr, FLR_E_CUDA, "list_metrics_static: cudaGetSymbolAddress returned a null address");
+        g_static_ptr[dev] = static_cast<double *>(ptr);
+        g_static_ready[dev] = true;
+    }
+    *out = g_static_ptr[dev];
+    return FLR_OK;
+}
+
+}  // namespace
+
+extern "C" int flr_list_metrics_static(const int32_t *neutral, const int32_t *neutral_len, const int32_t *lists,
+                                       const int32_t *lens, int64_t U, int V, int K, int k_cap, int vocab,
+                                       int empty_policy, int rank_metrics, int32_t *out_inter, int32_t *out_union,
+                                       float *out_jac, float *out_serp, float *out_prag, double *out_variant_sums,
+                                       int32_t *out_status, void *stream_) {
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    FLR_REQUIRE(U >= 0 && V >= 1 && K >= 1, FLR_E_INVALID, "list_metrics_static: need U>=0, V>=1, K>=1");
+    FLR_REQUIRE(k_cap >= 1, FLR_E_INVALID, "list_metrics_static: k_cap must be >= 1");
+    FLR_REQUIRE(empty_policy == FLR_EMPTY_ANY_IS_ZERO || empty_policy == FLR_EMPTY_BOTH_IS_ONE, FLR_E_INVALID,
+                "list_metrics_static: unknown empty_policy %d", empty_policy);
+    if (k_cap > K) k_cap = K;
+    FLR_REQUIRE(!rank_metrics || k_cap <= FLR_MAX_RANK_K, FLR_E_UNSUPPORTED,
+                "list_metrics_static: SERP*/PRAG* need k_cap <= %d (got %d)", FLR_MAX_RANK_K, k_cap);
+    FLR_REQUIRE(U * V < (1LL << 40), FLR_E_UNSUPPORTED, "list_metrics_static: too many pairs");
+    FLR_REQUIRE(U == 0 || (neutral && neutral_len && lists && lens), FLR_E_INVALID,
+                "list_metrics_static: null input pointer");
+
+    // How many partials this shape writes: 4 doubles per thread of the kernel that will run.
+    const Plan pl = make_plan(U, V, K, k_cap, vocab);
+    const size_t need = (pl.table ? static_cast<size_t>(pl.grid) * NT : static_cast<size_t>(pl.cmp_threads)) *
+                        4 * sizeof(double);
+    FLR_REQUIRE(need <= static_cast<size_t>(FLR_LIST_METRICS_STATIC_SCRATCH_BYTES), FLR_E_UNSUPPORTED,
+                "list_metrics_static: this shape needs %zu bytes of partial sums but the built-in scratch holds "
+                "%d; use flr_list_metrics with caller-provided scratch (U=%lld V=%d K=%d vocab=%d)",
+                need, FLR_LIST_METRICS_STATIC_SCRATCH_BYTES, static_cast<long long>(U), V, K, vocab);
+
+    double *partial = nullptr;
+    const int rc = static_scratch_for_current_device(&partial);
+    if (rc != FLR_OK) return rc;
+    if (U == 0) {
+        if (out_variant_sums) FLR_CUDA(cudaMemsetAsync(out_variant_sums, 0, sizeof(double) * 4 * V, stream));
+        return FLR_OK;
+    }
+    // Nothing in the array has to start at zero: every thread of the launch overwrites its own four
+    // partials before the reduction kernel reads them, and the reduction reads only those.  What the
+    // previous call left behind is never looked at, so nothing is cleared here.
+
+    LmParams p{};
+    p.neutral = neutral; p.neutral_len = neutral_len; p.lists = lists; p.lens = lens;
+    p.U = U; p.V = V; p.K = K; p.k_cap = k_cap; p.vocab = vocab; p.empty_policy = empty_policy;
+    p.out_inter = out_inter; p.out_union = out_union; p.out_jac = out_jac;
+    p.out_serp = out_serp; p.out_prag = out_prag;
+    p.partial = partial;
+    p.status = out_status;
+    p.vocab_pad = pl.vocab_pad; p.W = pl.W;
+
+    if (pl.table) {
+        p.T = pl.T;
+        p.use_bulk = (pl.T % 4 == 0) && aligned16(neutral) && aligned16(neutral_len) && aligned16(lists) &&
+                     aligned16(lens);
+        const int vec = (K % 4 == 0) ? 4 : (K % 2 == 0) ? 2 : 1;
+        void (*kern)(const LmParams) = nullptr;
+        if (rank_metrics) kern = vec == 4 ? list_metrics_table_kernel<4, true> : vec == 2 ? list_metrics_table_kernel<2, true> : list_metrics_table_kernel<1, true>;
+        else              kern = vec == 4 ? list_metrics_table_kernel<4, false> : vec == 2 ? list_metrics_table_kernel<2, false> : list_metrics_table_kernel<1, false>;
+        FLR_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(pl.smem)));
+        kern<<<pl.grid, NT, pl.smem, stream>>>(p);
+        FLR_LAUNCH_CHECK("list_metrics_table_kernel (static scratch)");
+        if (out_variant_sums) {
+            list_metrics_finalize_kernel<<<(V + 127) / 128, 128, 0, stream>>>(partial, pl.grid, NT, pl.T, V,
+                                                                               out_variant_sums);
+            FLR_LAUNCH_CHECK("list_metrics_finalize_kernel (static scratch)");
+        }
+    } else {
+        if (rank_metrics) list_metrics_cmp_kernel<true><<<pl.grid, CMP_THREADS, 0, stream>>>(p);
+        else              list_metrics_cmp_kernel<false><<<pl.grid, CMP_THREADS, 0, stream>>>(p);
+        FLR_LAUNCH_CHECK("list_metrics_cmp_kernel (static scratch)");
+        if (out_variant_sums) {
+            list_metrics_cmp_finalize_kernel<<<(V + 127) / 128, 128, 0, stream>>>(partial, pl.cmp_threads, V,
+                                                                                   out_variant_sums);
+            FLR_LAUNCH_CHECK("list_metrics_cmp_finalize_kernel (static scratch)");
         }
     }
     return FLR_OK;

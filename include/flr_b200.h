@@ -75,6 +75,38 @@ int flr_list_metrics(const int32_t *neutral, const int32_t *neutral_len,
                      double *out_variant_sums, int32_t *out_status,
                      void *scratch, size_t scratch_bytes, void *stream);
 
+/* flr_list_metrics for callers that cannot hand over a scratch buffer.  (No counterpart in the
+ * reference; it exists only because of how this library is embedded.)
+ *
+ * Some hosts run inside a memory plan they do not control: all of HBM already belongs to one
+ * pool, or the user shard was sized to fill the device, or the step loop must never meet the
+ * device-wide synchronisation a cudaMalloc brings.  They can pass inputs and outputs they
+ * already own, but not one more buffer.  This variant therefore takes no scratch argument and
+ * calls no allocating routine: the per-thread partial sums go to a fixed array compiled into
+ * the library (FLR_LIST_METRICS_STATIC_SCRATCH_BYTES; every GPU that loads the library holds
+ * that much until the process exits).
+ *
+ * Arguments and results are those of flr_list_metrics.  Limits and rules:
+ *   - a shape whose partial sums do not fit the array is refused with FLR_E_UNSUPPORTED and a
+ *     message naming both sizes.  Shapes served by the table kernel (2 <= V <= 128,
+ *     vocab <= 16384, k_cap <= 64) always fit on a B200, whatever U is; compare-kernel shapes
+ *     (V = 1 pair lists, larger vocabularies) fit up to about 65,000 pairs;
+ *   - the first call on a device looks up the array's device address
+ *     (cudaGetSymbolAddress, with that device current); make that first call before any stream
+ *     capture starts;
+ *   - all calls on a device share the one array and it keeps whatever the last call wrote.
+ *     Nothing in it needs to be zero at entry (each launch overwrites the partials it later
+ *     reads), but two calls whose kernels overlap on the GPU -- different streams, or
+ *     different host threads -- race on it.  Keep calls on one device in one stream order. */
+#define FLR_LIST_METRICS_STATIC_SCRATCH_BYTES 2097152
+int flr_list_metrics_static(const int32_t *neutral, const int32_t *neutral_len,
+                            const int32_t *lists, const int32_t *lens,
+                            int64_t U, int V, int K, int k_cap, int vocab,
+                            int empty_policy, int rank_metrics,
+                            int32_t *out_inter, int32_t *out_union,
+                            float *out_jac, float *out_serp, float *out_prag,
+                            double *out_variant_sums, int32_t *out_status, void *stream);
+
 /* All-pairs intersections between the M lists of each user (config 4 "pairwise
  * list-similarity"): 3706-bit item bitsets in shared memory, __popc over AND-ed words.
  *   lists int32 [U, M, K], lens int32 [U, M] -> out_inter int32 [U, M, M], out_sizes int32 [U, M]
