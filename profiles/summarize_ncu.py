@@ -1,0 +1,45 @@
+"""Summarise an ncu report (read here, on the CPU box):
+    python profiles/summarize_ncu.py gpurun_out/prof.ncu-rep profiles/rNN_name
+writes <out>_summary.csv (one row per captured launch, the metrics the roofline argument uses)
+and updates profiles/traffic.json (per-kernel DRAM bytes per launch, scaled note included)."""
+import csv, json, os, subprocess, sys
+
+KEYS = ["Kernel Name", "launch__grid_size", "launch__block_size", "launch__registers_per_thread",
+        "launch__occupancy_limit_registers", "launch__occupancy_limit_shared_mem", "gpu__time_duration.sum",
+        "dram__bytes_read.sum", "dram__bytes_write.sum", "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed",
+        "sm__throughput.avg.pct_of_peak_sustained_elapsed", "sm__warps_active.avg.pct_of_peak_sustained_active",
+        "smsp__issue_active.avg.pct_of_peak_sustained_active", "smsp__inst_executed.sum",
+        "sm__inst_executed_pipe_lsu.avg.pct_of_peak_sustained_active",
+        "sm__inst_executed_pipe_fp64.avg.pct_of_peak_sustained_active",
+        "l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum", "lts__throughput.avg.pct_of_peak_sustained_elapsed"]
+
+def main():
+    rep, out = sys.argv[1], sys.argv[2]
+    raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+    rows = list(csv.reader(raw.splitlines()))
+    hdr, units, data = rows[0], rows[1], rows[2:]
+    idx = {h: i for i, h in enumerate(hdr)}
+    keys = [k for k in KEYS if k in idx]
+    with open(out + "_summary.csv", "w", newline="") as f:
+        w = csv.writer(f)
+        w.writerow(keys)
+        w.writerow([units[idx[k]] for k in keys])
+        for r in data:
+            w.writerow([r[idx[k]] for k in keys])
+    def to_bytes(v, u):
+        return float(v) * {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "Tbyte": 1e12}[u]
+    traffic = {}
+    for r in data:
+        name = r[idx["Kernel Name"]]
+        short = "cosine_kernel" if "cosine_kernel" in name else "list_metrics_table_kernel" if "list_metrics_table" in name else name
+        b = (to_bytes(r[idx["dram__bytes_read.sum"]], units[idx["dram__bytes_read.sum"]]) +
+             to_bytes(r[idx["dram__bytes_write.sum"]], units[idx["dram__bytes_write.sum"]]))
+        traffic.setdefault(short, []).append(b)
+    tj = os.path.join(os.path.dirname(os.path.abspath(__file__)), "traffic.json")
+    note = sys.argv[3] if len(sys.argv) > 3 else ""
+    json.dump({"source": os.path.basename(out), "note": note,
+               "dram_bytes_per_launch": {k: sum(v) / len(v) for k, v in traffic.items()}}, open(tj, "w"), indent=1)
+    print(open(out + "_summary.csv").read())
+
+if __name__ == "__main__":
+    main()
