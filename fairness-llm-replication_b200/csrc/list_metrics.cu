@@ -266,18 +266,258 @@ __global__ void __launch_bounds__(NT, 2) list_metrics_table_kernel(const LmParam
     if (oov && p.status) atomicAdd(p.status, oov);
 }
 
-// Fixed-order reduction of the per-thread partials: thread v sums (block, slot) ascending.
-__global__ void list_metrics_finalize_kernel(const double *__restrict__ partial, int grid, int threads,
-                                             int T, int V, double *__restrict__ out) {
-    const int v = blockIdx.x * blockDim.x + threadIdx.x;
-    if (v >= V) return;
-    double a0 = 0, a1 = 0, a2 = 0, a3 = 0;
-    for (int b = 0; b < grid; ++b)
-        for (int s = 0; s < T; ++s) {
-            const double *q = partial + (static_cast<size_t>(b) * threads + s * V + v) * 4;
-            a0 += q[0]; a1 += q[1]; a2 += q[2]; a3 += q[3];
+// ---------------------------------------------------------------------------------------
+// Register kernel: the table kernel specialised for a compile-time row length KT (the
+// benchmark shapes K = 10, 20, 50).  Same data structures and results; what changes is the
+// schedule:
+//   * each thread copies its row from the staged tile into registers and the CTA immediately
+//     re-arms the bulk TMA copy of its NEXT tile into the same buffer, so the HBM read of tile
+//     i+1 overlaps all the work on tile i;
+//   * all KT rank look-ups are issued back to back (independent loads) and packed beside the
+//     ids; the only serial chain left per element is the private bit set's load -> store;
+//   * every loop over the row is fully unrolled.
+// ---------------------------------------------------------------------------------------
+template <int KT, bool RANK>
+__global__ void __launch_bounds__(NT, 2) list_metrics_reg_kernel(const LmParams p) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    const LmSmem L = lm_layout(p.T, p.V, KT, p.vocab_pad, p.W);
+    uint64_t *bar = reinterpret_cast<uint64_t *>(smem);
+    int32_t *s_lists = reinterpret_cast<int32_t *>(smem + L.off_lists);
+    int32_t *s_neutral = reinterpret_cast<int32_t *>(smem + L.off_neutral);
+    int32_t *s_lens = reinterpret_cast<int32_t *>(smem + L.off_lens);
+    int32_t *s_nlen = reinterpret_cast<int32_t *>(smem + L.off_nlen);
+    int32_t *s_na = reinterpret_cast<int32_t *>(smem + L.off_na);
+    uint8_t *s_tab = smem + L.off_tab;
+    uint32_t *s_bits = reinterpret_cast<uint32_t *>(smem + L.off_bits);
+    int32_t *s_keep = reinterpret_cast<int32_t *>(smem + L.total);          // [T][KT] neutral ids of the live tile
+    int32_t *s_keep_len = s_keep + p.T * KT;                                  // [T]
+
+    constexpr int VEC = (KT % 4 == 0) ? 4 : 2;
+    static_assert(KT % 2 == 0 && KT <= 64, "row length must be even and fit the rank mask");
+
+    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    const int V = p.V, T = p.T, Kn = p.k_cap;
+    const unsigned vocab = static_cast<unsigned>(p.vocab);
+    const int pairs_per_tile = T * V;
+    const int slot = t / V;
+    const bool pair_thread = t < pairs_per_tile;
+
+    {
+        int4 *tab4 = reinterpret_cast<int4 *>(s_tab);
+        const int n4 = T * p.vocab_pad / 16;
+        for (int i = t; i < n4; i += NT) tab4[i] = make_int4(-1, -1, -1, -1);
+        for (int w = 0; w < p.W; ++w) s_bits[w * NT + t] = 0u;
+        if (t == 0) {
+            mbar_init(bar, 1);
+            fence_mbar_init();
         }
-    out[v * 4 + 0] = a0; out[v * 4 + 1] = a1; out[v * 4 + 2] = a2; out[v * 4 + 3] = a3;
+    }
+    __syncthreads();
+
+    const int64_t n_tiles = (p.U + T - 1) / T;
+    const uint32_t bytes_lists = static_cast<uint32_t>(T) * V * KT * 4, bytes_neutral = static_cast<uint32_t>(T) * KT * 4;
+    const uint32_t bytes_lens = static_cast<uint32_t>(T) * V * 4, bytes_nlen = static_cast<uint32_t>(T) * 4;
+    auto issue_tma = [&](int64_t tile) {       // thread 0 only; the stage buffer must be free
+        const int64_t u0 = tile * T;
+        fence_proxy_async();
+        mbar_expect_tx(bar, bytes_lists + bytes_neutral + bytes_lens + bytes_nlen);
+        bulk_g2s(s_lists, p.lists + u0 * V * KT, bytes_lists, bar);
+        bulk_g2s(s_neutral, p.neutral + u0 * KT, bytes_neutral, bar);
+        bulk_g2s(s_lens, p.lens + u0 * V, bytes_lens, bar);
+        bulk_g2s(s_nlen, p.neutral_len + u0, bytes_nlen, bar);
+    };
+    auto tile_is_bulk = [&](int64_t tile) { return p.use_bulk && tile < n_tiles && (tile + 1) * T <= p.U; };
+
+    uint32_t phase = 0;
+    double acc_j = 0.0;
+    long long acc_s = 0, acc_p = 0;
+    int acc_n = 0, oov = 0;
+    if (t == 0 && tile_is_bulk(blockIdx.x)) issue_tma(blockIdx.x);
+
+    for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        const int64_t u0 = tile * T;
+        const int tu = static_cast<int>(min(static_cast<int64_t>(T), p.U - u0));
+        if (tile_is_bulk(tile)) {
+            mbar_wait(bar, phase);
+            phase ^= 1u;
+        } else {
+            const int32_t *gl = p.lists + u0 * V * KT;
+            for (int i = t; i < tu * V * KT; i += NT) s_lists[i] = gl[i];
+            const int32_t *gn = p.neutral + u0 * KT;
+            for (int i = t; i < tu * KT; i += NT) s_neutral[i] = gn[i];
+            for (int i = t; i < tu * V; i += NT) s_lens[i] = p.lens[u0 * V + i];
+            for (int i = t; i < tu; i += NT) s_nlen[i] = p.neutral_len[u0 + i];
+            __syncthreads();
+        }
+
+        // ---- move the tile out of the stage buffer: own row -> registers, neutral lists -> s_keep ----
+        unsigned ids[KT];
+        int Kb = 0;
+        const bool live = pair_thread && slot < tu;
+        if (live) {
+            Kb = max(0, min(s_lens[t], Kn));
+            const int32_t *row = s_lists + t * KT;
+#pragma unroll
+            for (int j0 = 0; j0 < KT; j0 += VEC) {
+                int tmp[VEC];
+                load_ids<VEC>(row + j0, tmp);
+#pragma unroll
+                for (int e = 0; e < VEC; ++e) ids[j0 + e] = static_cast<unsigned>(tmp[e]);
+            }
+        }
+        for (int i = t; i < tu * KT; i += NT) s_keep[i] = s_neutral[i];
+        for (int i = t; i < tu; i += NT) s_keep_len[i] = max(0, min(s_nlen[i], Kn));
+        __syncthreads();
+        if (t == 0 && tile_is_bulk(tile + gridDim.x)) issue_tma(tile + gridDim.x);   // overlaps everything below
+
+        // ---- rank tables ----
+        for (int s = warp; s < tu; s += NT / 32) {
+            const int Ka = s_keep_len[s];
+            const int32_t *A = s_keep + s * KT;
+            uint8_t *tab = s_tab + s * p.vocab_pad;
+            for (int base = ((Ka - 1) >> 5) << 5; base >= 0; base -= 32) {
+                const int j = base + lane;
+                if (j < Ka) {
+                    const unsigned id = static_cast<unsigned>(A[j]);
+                    if (id < vocab) tab[id] = static_cast<uint8_t>(j); else ++oov;
+                }
+                __syncwarp();
+            }
+            bool again;
+            do {
+                again = false;
+                for (int base = 0; base < Ka; base += 32) {
+                    const int j = base + lane;
+                    if (j < Ka) {
+                        const unsigned id = static_cast<unsigned>(A[j]);
+                        if (id < vocab && tab[id] > j) { tab[id] = static_cast<uint8_t>(j); again = true; }
+                    }
+                }
+                __syncwarp();
+                again = __any_sync(0xffffffffu, again);
+            } while (again);
+            int cnt = 0;
+            for (int base = 0; base < Ka; base += 32) {
+                const int j = base + lane;
+                bool first = false;
+                if (j < Ka) {
+                    const unsigned id = static_cast<unsigned>(A[j]);
+                    first = id < vocab && tab[id] == j;
+                }
+                cnt += __popc(__ballot_sync(0xffffffffu, first));
+            }
+            if (lane == 0) s_na[s] = cnt;
+        }
+        __syncthreads();
+
+        if (live) {
+            const uint8_t *tab = s_tab + slot * p.vocab_pad;
+            // phase A: all rank look-ups, independent of one another.  ids[j] is repacked as
+            //   bits 0-15  byte offset of the element's word in the private bit set ((id >> 5) * NT * 4)
+            //   bits 16-20 bit position (id & 31)      bits 21-28 rank in the neutral list (0xFF absent)
+            //   bit 31     element is not part of the row (padding, cut by k_cap, or out of vocabulary)
+            // An excluded element points at word 0 with an empty bit, so phase B needs no branch.
+        #pragma unroll
+            for (int j = 0; j < KT; ++j) {
+                const unsigned id = ids[j];
+                const bool in_row = j < Kb;
+                const bool ok = in_row && id < vocab;
+                oov += (in_row && !ok) ? 1 : 0;
+                const unsigned idc = ok ? id : 0u;
+                const unsigned r = tab[idc];
+                ids[j] = ((idc >> 5) * (NT * 4)) | ((idc & 31u) << 16) | (r << 21) | (ok ? 0u : 0x80000000u);
+            }
+            // phase B: duplicate test through the private bit set + metric updates, branch-free
+            const char *bits_base = reinterpret_cast<const char *>(s_bits + t);
+            uint64_t seen2 = 0;                      // (mask of neutral ranks already hit) << 1
+            int n_b = 0, inter = 0, serp = 0, prag = 0;
+#pragma unroll
+            for (int j = 0; j < KT; ++j) {
+                const unsigned x = ids[j];
+                uint32_t *wp = reinterpret_cast<uint32_t *>(const_cast<char *>(bits_base) + (x & 0xFFFFu));
+                const uint32_t w = *wp;
+                const uint32_t b = (x >> 31) ? 0u : (1u << ((x >> 16) & 31u));
+                *wp = w | b;
+                const bool first = (b & ~w) != 0u;                       // a live element whose bit was clear
+                const unsigned r = (x >> 21) & 0xFFu;
+                const bool hit = first && r != 0xFFu;
+                n_b += first ? 1 : 0;
+                if constexpr (RANK) {
+                    const unsigned rr = r & 63u;
+                    const int below = __popcll(seen2 << (63u - rr));     // earlier hits with a smaller rank
+                    prag += hit ? below : (first ? inter : 0);            // absent item: every earlier hit counts
+                    serp += hit ? (Kn - j) : 0;
+                    seen2 |= hit ? (2ull << rr) : 0ull;
+                }
+                inter += hit ? 1 : 0;
+            }
+            const int n_a = s_na[slot];
+            const int uni = n_a + n_b - inter;
+            double jac;
+            if (p.empty_policy == FLR_EMPTY_BOTH_IS_ONE)
+                jac = uni > 0 ? static_cast<double>(inter) / static_cast<double>(uni) : 1.0;
+            else
+                jac = (n_a == 0 || n_b == 0) ? 0.0 : static_cast<double>(inter) / static_cast<double>(uni);
+            const int64_t pair = u0 * V + t;
+            if (p.out_inter) p.out_inter[pair] = inter;
+            if (p.out_union) p.out_union[pair] = uni;
+            if (p.out_jac) p.out_jac[pair] = static_cast<float>(jac);
+            if constexpr (RANK) {
+                if (p.out_serp) p.out_serp[pair] = static_cast<float>(serp) / static_cast<float>(Kn * (Kn + 1) / 2);
+                if (p.out_prag) p.out_prag[pair] = static_cast<float>(prag) / static_cast<float>(Kn * (Kn + 1));
+            }
+            acc_j += jac;
+            acc_s += serp;
+            acc_p += prag;
+            acc_n += 1;
+            // wipe the private bit set (word offsets are still in registers)
+#pragma unroll
+            for (int j = 0; j < KT; ++j)
+                *reinterpret_cast<uint32_t *>(const_cast<char *>(bits_base) + (ids[j] & 0xFFFFu)) = 0u;
+        }
+        __syncthreads();
+
+        for (int s = warp; s < tu; s += NT / 32) {
+            const int Ka = s_keep_len[s];
+            const int32_t *A = s_keep + s * KT;
+            uint8_t *tab = s_tab + s * p.vocab_pad;
+            for (int j = lane; j < Ka; j += 32) {
+                const unsigned id = static_cast<unsigned>(A[j]);
+                if (id < vocab) tab[id] = 0xFFu;
+            }
+        }
+        __syncthreads();
+    }
+
+    double *dst = p.partial + (static_cast<size_t>(blockIdx.x) * NT + t) * 4;
+    dst[0] = acc_j;
+    dst[1] = static_cast<double>(acc_s);
+    dst[2] = static_cast<double>(acc_p);
+    dst[3] = static_cast<double>(acc_n);
+    if (oov && p.status) atomicAdd(p.status, oov);
+}
+
+// Fixed-order reduction of the per-thread partials, one warp per variant: lane l adds the
+// (block, slot) entries l, l+32, ... in ascending order, then an xor butterfly -- the order
+// depends only on the launch geometry, so the sums are bit-reproducible.
+__global__ void __launch_bounds__(128) list_metrics_finalize_kernel(const double *__restrict__ partial, int grid,
+                                                                    int threads, int T, int V,
+                                                                    double *__restrict__ out) {
+    const int v = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (v >= V) return;
+    double a[4] = {0, 0, 0, 0};
+    const int n = grid * T;
+    for (int e = lane; e < n; e += 32) {
+        const int b = e / T, sl = e - b * T;
+        const double4 *q = reinterpret_cast<const double4 *>(partial + (static_cast<size_t>(b) * threads + sl * V + v) * 4);
+        const double4 lo = *q;
+        a[0] += lo.x; a[1] += lo.y; a[2] += lo.z; a[3] += lo.w;
+    }
+#pragma unroll
+    for (int off = 16; off >= 1; off >>= 1)
+#pragma unroll
+        for (int k = 0; k < 4; ++k) a[k] += __shfl_xor_sync(0xffffffffu, a[k], off);
+    if (lane == 0) { out[v * 4 + 0] = a[0]; out[v * 4 + 1] = a[1]; out[v * 4 + 2] = a[2]; out[v * 4 + 3] = a[3]; }
 }
 
 // ---------------------------------------------------------------------------------------
@@ -355,21 +595,33 @@ __global__ void __launch_bounds__(CMP_THREADS) list_metrics_cmp_kernel(const LmP
     if (oov && p.status) atomicAdd(p.status, oov);
 }
 
-// thread v sums the partials of all threads whose first pair has variant v (index = v mod V)
-__global__ void list_metrics_cmp_finalize_kernel(const double *__restrict__ partial, int64_t n_threads, int V,
-                                                 double *__restrict__ out) {
-    const int v = blockIdx.x * blockDim.x + threadIdx.x;
-    if (v >= V) return;
-    double a0 = 0, a1 = 0, a2 = 0, a3 = 0;
-    for (int64_t i = v; i < n_threads; i += V) {
+// Block v sums the partials of all threads whose first pair has variant v (index = v mod V):
+// thread t takes every 256th of them in ascending order, then a fixed shared-memory tree.
+__global__ void __launch_bounds__(256) list_metrics_cmp_finalize_kernel(const double *__restrict__ partial,
+                                                                        int64_t n_threads, int V,
+                                                                        double *__restrict__ out) {
+    __shared__ double s_acc[256][4];
+    const int v = blockIdx.x, t = threadIdx.x;
+    double a[4] = {0, 0, 0, 0};
+    for (int64_t i = v + static_cast<int64_t>(V) * t; i < n_threads; i += static_cast<int64_t>(V) * 256) {
         const double *q = partial + i * 4;
-        a0 += q[0]; a1 += q[1]; a2 += q[2]; a3 += q[3];
+        a[0] += q[0]; a[1] += q[1]; a[2] += q[2]; a[3] += q[3];
     }
-    out[v * 4 + 0] = a0; out[v * 4 + 1] = a1; out[v * 4 + 2] = a2; out[v * 4 + 3] = a3;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) s_acc[t][k] = a[k];
+    __syncthreads();
+    for (int half = 128; half >= 1; half >>= 1) {
+        if (t < half)
+#pragma unroll
+            for (int k = 0; k < 4; ++k) s_acc[t][k] += s_acc[t + half][k];
+        __syncthreads();
+    }
+    if (t < 4) out[v * 4 + t] = s_acc[0][t];
 }
 
 struct Plan {
-    bool table;
+    bool table;        // table / register kernel (else compare kernel)
+    int reg_k;         // compile-time row length of the register kernel, 0 = generic table kernel
     int T, vocab_pad, W, grid;
     size_t smem;
     int64_t cmp_threads;
@@ -382,14 +634,18 @@ Plan make_plan(int64_t U, int V, int K, int k_cap, int vocab) {
     pl.W = (vocab + 31) / 32;
     pl.table = false;
     if (vocab > 0 && vocab <= 16384 && k_cap <= FLR_MAX_RANK_K && V >= 2 && V <= NT) {
+        const bool reg = (K == 10 || K == 20 || K == 50);
+        const size_t extra = reg ? align16(static_cast<size_t>(1) * K * 4 + 4) : 0;     // per user slot
+        auto bytes = [&](int T) { return lm_layout(T, V, K, pl.vocab_pad, pl.W).total + (reg ? align16(extra * T) : 0); };
         int T = NT / V;
         if (T >= 4) T &= ~3;                 // multiples of 4 keep every bulk copy 16-byte sized
-        while (T >= 1 && lm_layout(T, V, K, pl.vocab_pad, pl.W).total > static_cast<size_t>(kTableSmemBudget))
+        while (T >= 1 && bytes(T) > static_cast<size_t>(kTableSmemBudget))
             T = (T > 4) ? ((T - 1) & ~3) : T - 1;
         if (T >= 1 && T * V * 2 >= NT) {      // at least half of the CTA's threads own a pair
             pl.table = true;
+            pl.reg_k = reg ? K : 0;
             pl.T = T;
-            pl.smem = lm_layout(T, V, K, pl.vocab_pad, pl.W).total;
+            pl.smem = bytes(T);
             const int64_t tiles = (U + T - 1) / T;
             pl.grid = static_cast<int>(std::min<int64_t>(std::max<int64_t>(tiles, 1), 2LL * sms));
         }
@@ -403,6 +659,82 @@ Plan make_plan(int64_t U, int V, int K, int k_cap, int vocab) {
         pl.cmp_threads = blocks * CMP_THREADS;
     }
     return pl;
+}
+
+// Bytes of per-thread partial sums the planned launch writes (4 doubles per thread).
+size_t partial_bytes(const Plan &pl) {
+    return (pl.table ? static_cast<size_t>(pl.grid) * NT : static_cast<size_t>(pl.cmp_threads)) * 4 * sizeof(double);
+}
+
+using TableKernel = void (*)(const LmParams);
+
+TableKernel pick_table_kernel(const Plan &pl, int K, bool rank) {
+    switch (pl.reg_k) {
+        case 10: return rank ? list_metrics_reg_kernel<10, true> : list_metrics_reg_kernel<10, false>;
+        case 20: return rank ? list_metrics_reg_kernel<20, true> : list_metrics_reg_kernel<20, false>;
+        case 50: return rank ? list_metrics_reg_kernel<50, true> : list_metrics_reg_kernel<50, false>;
+        default: break;
+    }
+    const int vec = (K % 4 == 0) ? 4 : (K % 2 == 0) ? 2 : 1;
+    if (rank) return vec == 4 ? list_metrics_table_kernel<4, true> : vec == 2 ? list_metrics_table_kernel<2, true> : list_metrics_table_kernel<1, true>;
+    return vec == 4 ? list_metrics_table_kernel<4, false> : vec == 2 ? list_metrics_table_kernel<2, false> : list_metrics_table_kernel<1, false>;
+}
+
+int check_args(const char *who, const int32_t *neutral, const int32_t *neutral_len, const int32_t *lists,
+               const int32_t *lens, int64_t U, int V, int K, int &k_cap, int empty_policy, int rank_metrics) {
+    FLR_REQUIRE(U >= 0 && V >= 1 && K >= 1, FLR_E_INVALID, "%s: need U>=0, V>=1, K>=1", who);
+    FLR_REQUIRE(k_cap >= 1, FLR_E_INVALID, "%s: k_cap must be >= 1", who);
+    FLR_REQUIRE(empty_policy == FLR_EMPTY_ANY_IS_ZERO || empty_policy == FLR_EMPTY_BOTH_IS_ONE, FLR_E_INVALID,
+                "%s: unknown empty_policy %d", who, empty_policy);
+    if (k_cap > K) k_cap = K;
+    FLR_REQUIRE(!rank_metrics || k_cap <= FLR_MAX_RANK_K, FLR_E_UNSUPPORTED,
+                "%s: SERP*/PRAG* need k_cap <= %d (got %d)", who, FLR_MAX_RANK_K, k_cap);
+    FLR_REQUIRE(U * V < (1LL << 40), FLR_E_UNSUPPORTED, "%s: too many pairs", who);
+    FLR_REQUIRE(U == 0 || (neutral && neutral_len && lists && lens), FLR_E_INVALID, "%s: null input pointer", who);
+    return FLR_OK;
+}
+
+// Launches the planned kernels; `partial` must hold partial_bytes(pl).
+int launch_planned(const Plan &pl, LmParams p, int rank_metrics, double *out_variant_sums, cudaStream_t stream) {
+    p.vocab_pad = pl.vocab_pad;
+    p.W = pl.W;
+    if (pl.table) {
+        p.T = pl.T;
+        p.use_bulk = (pl.T % 4 == 0) && aligned16(p.neutral) && aligned16(p.neutral_len) && aligned16(p.lists) &&
+                     aligned16(p.lens);
+        TableKernel kern = pick_table_kernel(pl, p.K, rank_metrics != 0);
+        FLR_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(pl.smem)));
+        kern<<<pl.grid, NT, pl.smem, stream>>>(p);
+        FLR_LAUNCH_CHECK("list_metrics table/register kernel");
+        if (out_variant_sums) {
+            list_metrics_finalize_kernel<<<(p.V + 3) / 4, 128, 0, stream>>>(p.partial, pl.grid, NT, pl.T, p.V,
+                                                                             out_variant_sums);
+            FLR_LAUNCH_CHECK("list_metrics_finalize_kernel");
+        }
+    } else {
+        if (rank_metrics) list_metrics_cmp_kernel<true><<<pl.grid, CMP_THREADS, 0, stream>>>(p);
+        else              list_metrics_cmp_kernel<false><<<pl.grid, CMP_THREADS, 0, stream>>>(p);
+        FLR_LAUNCH_CHECK("list_metrics_cmp_kernel");
+        if (out_variant_sums) {
+            list_metrics_cmp_finalize_kernel<<<p.V, 256, 0, stream>>>(p.partial, pl.cmp_threads, p.V, out_variant_sums);
+            FLR_LAUNCH_CHECK("list_metrics_cmp_finalize_kernel");
+        }
+    }
+    return FLR_OK;
+}
+
+LmParams make_params(const int32_t *neutral, const int32_t *neutral_len, const int32_t *lists, const int32_t *lens,
+                     int64_t U, int V, int K, int k_cap, int vocab, int empty_policy, int32_t *out_inter,
+                     int32_t *out_union, float *out_jac, float *out_serp, float *out_prag, int32_t *out_status,
+                     double *partial) {
+    LmParams p{};
+    p.neutral = neutral; p.neutral_len = neutral_len; p.lists = lists; p.lens = lens;
+    p.U = U; p.V = V; p.K = K; p.k_cap = k_cap; p.vocab = vocab; p.empty_policy = empty_policy;
+    p.out_inter = out_inter; p.out_union = out_union; p.out_jac = out_jac;
+    p.out_serp = out_serp; p.out_prag = out_prag;
+    p.partial = partial;
+    p.status = out_status;
+    return p;
 }
 
 }  // namespace
@@ -426,60 +758,21 @@ extern "C" int flr_list_metrics(const int32_t *neutral, const int32_t *neutral_l
                                 float *out_jac, float *out_serp, float *out_prag, double *out_variant_sums,
                                 int32_t *out_status, void *scratch, size_t scratch_bytes, void *stream_) {
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
-    FLR_REQUIRE(U >= 0 && V >= 1 && K >= 1, FLR_E_INVALID, "list_metrics: need U>=0, V>=1, K>=1");
-    FLR_REQUIRE(k_cap >= 1, FLR_E_INVALID, "list_metrics: k_cap must be >= 1");
-    FLR_REQUIRE(empty_policy == FLR_EMPTY_ANY_IS_ZERO || empty_policy == FLR_EMPTY_BOTH_IS_ONE, FLR_E_INVALID,
-                "list_metrics: unknown empty_policy %d", empty_policy);
-    if (k_cap > K) k_cap = K;
-    FLR_REQUIRE(!rank_metrics || k_cap <= FLR_MAX_RANK_K, FLR_E_UNSUPPORTED,
-                "list_metrics: SERP*/PRAG* need k_cap <= %d (got %d)", FLR_MAX_RANK_K, k_cap);
-    FLR_REQUIRE(U * V < (1LL << 40), FLR_E_UNSUPPORTED, "list_metrics: too many pairs");
+    const int rc = check_args("list_metrics", neutral, neutral_len, lists, lens, U, V, K, k_cap, empty_policy,
+                              rank_metrics);
+    if (rc != FLR_OK) return rc;
     if (U == 0) {
         if (out_variant_sums) FLR_CUDA(cudaMemsetAsync(out_variant_sums, 0, sizeof(double) * 4 * V, stream));
         return FLR_OK;
     }
-    FLR_REQUIRE(neutral && neutral_len && lists && lens, FLR_E_INVALID, "list_metrics: null input pointer");
     FLR_REQUIRE(scratch && scratch_bytes >= flr_list_metrics_scratch_bytes(U, V, K, vocab), FLR_E_SCRATCH,
                 "list_metrics: scratch too small (%zu < %zu)", scratch_bytes,
                 flr_list_metrics_scratch_bytes(U, V, K, vocab));
-
     const Plan pl = make_plan(U, V, K, k_cap, vocab);
-    LmParams p{};
-    p.neutral = neutral; p.neutral_len = neutral_len; p.lists = lists; p.lens = lens;
-    p.U = U; p.V = V; p.K = K; p.k_cap = k_cap; p.vocab = vocab; p.empty_policy = empty_policy;
-    p.out_inter = out_inter; p.out_union = out_union; p.out_jac = out_jac;
-    p.out_serp = out_serp; p.out_prag = out_prag;
-    p.partial = static_cast<double *>(scratch);
-    p.status = out_status;
-    p.vocab_pad = pl.vocab_pad; p.W = pl.W;
-
-    if (pl.table) {
-        p.T = pl.T;
-        p.use_bulk = (pl.T % 4 == 0) && aligned16(neutral) && aligned16(neutral_len) && aligned16(lists) &&
-                     aligned16(lens);
-        const int vec = (K % 4 == 0) ? 4 : (K % 2 == 0) ? 2 : 1;
-        void (*kern)(const LmParams) = nullptr;
-        if (rank_metrics) kern = vec == 4 ? list_metrics_table_kernel<4, true> : vec == 2 ? list_metrics_table_kernel<2, true> : list_metrics_table_kernel<1, true>;
-        else              kern = vec == 4 ? list_metrics_table_kernel<4, false> : vec == 2 ? list_metrics_table_kernel<2, false> : list_metrics_table_kernel<1, false>;
-        FLR_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(pl.smem)));
-        kern<<<pl.grid, NT, pl.smem, stream>>>(p);
-        FLR_LAUNCH_CHECK("list_metrics_table_kernel");
-        if (out_variant_sums) {
-            list_metrics_finalize_kernel<<<(V + 127) / 128, 128, 0, stream>>>(p.partial, pl.grid, NT, pl.T, V,
-                                                                               out_variant_sums);
-            FLR_LAUNCH_CHECK("list_metrics_finalize_kernel");
-        }
-    } else {
-        if (rank_metrics) list_metrics_cmp_kernel<true><<<pl.grid, CMP_THREADS, 0, stream>>>(p);
-        else              list_metrics_cmp_kernel<false><<<pl.grid, CMP_THREADS, 0, stream>>>(p);
-        FLR_LAUNCH_CHECK("list_metrics_cmp_kernel");
-        if (out_variant_sums) {
-            list_metrics_cmp_finalize_kernel<<<(V + 127) / 128, 128, 0, stream>>>(p.partial, pl.cmp_threads, V,
-                                                                                   out_variant_sums);
-            FLR_LAUNCH_CHECK("list_metrics_cmp_finalize_kernel");
-        }
-    }
-    return FLR_OK;
+    return launch_planned(pl, make_params(neutral, neutral_len, lists, lens, U, V, K, k_cap, vocab, empty_policy,
+                                          out_inter, out_union, out_jac, out_serp, out_prag, out_status,
+                                          static_cast<double *>(scratch)),
+                          rank_metrics, out_variant_sums, stream);
 }
 
 // ---------------------------------------------------------------------------------------
@@ -532,28 +825,20 @@ extern "C" int flr_list_metrics_static(const int32_t *neutral, const int32_t *ne
                                        float *out_jac, float *out_serp, float *out_prag, double *out_variant_sums,
                                        int32_t *out_status, void *stream_) {
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
-    FLR_REQUIRE(U >= 0 && V >= 1 && K >= 1, FLR_E_INVALID, "list_metrics_static: need U>=0, V>=1, K>=1");
-    FLR_REQUIRE(k_cap >= 1, FLR_E_INVALID, "list_metrics_static: k_cap must be >= 1");
-    FLR_REQUIRE(empty_policy == FLR_EMPTY_ANY_IS_ZERO || empty_policy == FLR_EMPTY_BOTH_IS_ONE, FLR_E_INVALID,
-                "list_metrics_static: unknown empty_policy %d", empty_policy);
-    if (k_cap > K) k_cap = K;
-    FLR_REQUIRE(!rank_metrics || k_cap <= FLR_MAX_RANK_K, FLR_E_UNSUPPORTED,
-                "list_metrics_static: SERP*/PRAG* need k_cap <= %d (got %d)", FLR_MAX_RANK_K, k_cap);
-    FLR_REQUIRE(U * V < (1LL << 40), FLR_E_UNSUPPORTED, "list_metrics_static: too many pairs");
-    FLR_REQUIRE(U == 0 || (neutral && neutral_len && lists && lens), FLR_E_INVALID,
-                "list_metrics_static: null input pointer");
+    int rc = check_args("list_metrics_static", neutral, neutral_len, lists, lens, U, V, K, k_cap, empty_policy,
+                        rank_metrics);
+    if (rc != FLR_OK) return rc;
 
     // How many partials this shape writes: 4 doubles per thread of the kernel that will run.
     const Plan pl = make_plan(U, V, K, k_cap, vocab);
-    const size_t need = (pl.table ? static_cast<size_t>(pl.grid) * NT : static_cast<size_t>(pl.cmp_threads)) *
-                        4 * sizeof(double);
+    const size_t need = partial_bytes(pl);
     FLR_REQUIRE(need <= static_cast<size_t>(FLR_LIST_METRICS_STATIC_SCRATCH_BYTES), FLR_E_UNSUPPORTED,
                 "list_metrics_static: this shape needs %zu bytes of partial sums but the built-in scratch holds "
                 "%d; use flr_list_metrics with caller-provided scratch (U=%lld V=%d K=%d vocab=%d)",
                 need, FLR_LIST_METRICS_STATIC_SCRATCH_BYTES, static_cast<long long>(U), V, K, vocab);
 
     double *partial = nullptr;
-    const int rc = static_scratch_for_current_device(&partial);
+    rc = static_scratch_for_current_device(&partial);
     if (rc != FLR_OK) return rc;
     if (U == 0) {
         if (out_variant_sums) FLR_CUDA(cudaMemsetAsync(out_variant_sums, 0, sizeof(double) * 4 * V, stream));
@@ -562,41 +847,7 @@ extern "C" int flr_list_metrics_static(const int32_t *neutral, const int32_t *ne
     // Nothing in the array has to start at zero: every thread of the launch overwrites its own four
     // partials before the reduction kernel reads them, and the reduction reads only those.  What the
     // previous call left behind is never looked at, so nothing is cleared here.
-
-    LmParams p{};
-    p.neutral = neutral; p.neutral_len = neutral_len; p.lists = lists; p.lens = lens;
-    p.U = U; p.V = V; p.K = K; p.k_cap = k_cap; p.vocab = vocab; p.empty_policy = empty_policy;
-    p.out_inter = out_inter; p.out_union = out_union; p.out_jac = out_jac;
-    p.out_serp = out_serp; p.out_prag = out_prag;
-    p.partial = partial;
-    p.status = out_status;
-    p.vocab_pad = pl.vocab_pad; p.W = pl.W;
-
-    if (pl.table) {
-        p.T = pl.T;
-        p.use_bulk = (pl.T % 4 == 0) && aligned16(neutral) && aligned16(neutral_len) && aligned16(lists) &&
-                     aligned16(lens);
-        const int vec = (K % 4 == 0) ? 4 : (K % 2 == 0) ? 2 : 1;
-        void (*kern)(const LmParams) = nullptr;
-        if (rank_metrics) kern = vec == 4 ? list_metrics_table_kernel<4, true> : vec == 2 ? list_metrics_table_kernel<2, true> : list_metrics_table_kernel<1, true>;
-        else              kern = vec == 4 ? list_metrics_table_kernel<4, false> : vec == 2 ? list_metrics_table_kernel<2, false> : list_metrics_table_kernel<1, false>;
-        FLR_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(pl.smem)));
-        kern<<<pl.grid, NT, pl.smem, stream>>>(p);
-        FLR_LAUNCH_CHECK("list_metrics_table_kernel (static scratch)");
-        if (out_variant_sums) {
-            list_metrics_finalize_kernel<<<(V + 127) / 128, 128, 0, stream>>>(partial, pl.grid, NT, pl.T, V,
-                                                                               out_variant_sums);
-            FLR_LAUNCH_CHECK("list_metrics_finalize_kernel (static scratch)");
-        }
-    } else {
-        if (rank_metrics) list_metrics_cmp_kernel<true><<<pl.grid, CMP_THREADS, 0, stream>>>(p);
-        else              list_metrics_cmp_kernel<false><<<pl.grid, CMP_THREADS, 0, stream>>>(p);
-        FLR_LAUNCH_CHECK("list_metrics_cmp_kernel (static scratch)");
-        if (out_variant_sums) {
-            list_metrics_cmp_finalize_kernel<<<(V + 127) / 128, 128, 0, stream>>>(partial, pl.cmp_threads, V,
-                                                                                   out_variant_sums);
-            FLR_LAUNCH_CHECK("list_metrics_cmp_finalize_kernel (static scratch)");
-        }
-    }
-    return FLR_OK;
+    return launch_planned(pl, make_params(neutral, neutral_len, lists, lens, U, V, K, k_cap, vocab, empty_policy,
+                                          out_inter, out_union, out_jac, out_serp, out_prag, out_status, partial),
+                          rank_metrics, out_variant_sums, stream);
 }
