@@ -134,9 +134,289 @@ __global__ void __launch_bounds__(COS_THREADS) cosine_kernel(const float *__rest
     }
 }
 
+// ---------------------------------------------------------------------------------------
+// TMA-pipelined form (the fast path).  One persistent CTA per SM: a producer thread streams
+// groups of G users -- the anchor rows and the G*V counterfactual rows are each one contiguous
+// block of HBM -- into a ring of shared-memory stages with bulk TMA copies (cp.async.bulk +
+// mbarrier tx-count); eight consumer warps take batches of four rows out of the stage that
+// just landed.  HBM requests are therefore always RING bytes deep per SM (~190 KB),
+// independent of what the consumers are doing.  The arithmetic is the one described at the
+// top of this file, bit for bit: lane-strided fp64 accumulation, xor butterfly 16,8,4,2,1 --
+// the butterfly is "transposed" (eight running sums are halved at each step instead of all
+// being shuffled), which pairs exactly the same operands.
+// ---------------------------------------------------------------------------------------
+constexpr int TMA_CONSUMER_WARPS = 8;
+constexpr int TMA_THREADS = (TMA_CONSUMER_WARPS + 1) * 32;
+constexpr int TMA_MAX_STAGES = 4;
+
+struct CosTmaParams {
+    const float *a, *b;
+    int64_t U;
+    int V, D, G, stages;
+    uint32_t stage_bytes, a_bytes;       // per stage: [a chunk | b chunk], a_bytes = G*D*4 rounded to 128
+    float *out;
+    unsigned long long *hist0;
+};
+
+template <int NC>
+__device__ __forceinline__ void load_row_f64(const float *row, int lane, int nchunk, double (&v)[NC][4]) {
+#pragma unroll
+    for (int c = 0; c < NC; ++c) {
+        const int ch = lane + 32 * c;
+        float4 q = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (ch < nchunk) q = *reinterpret_cast<const float4 *>(row + 4 * ch);
+        v[c][0] = q.x; v[c][1] = q.y; v[c][2] = q.z; v[c][3] = q.w;
+    }
+}
+
+// Reduce the eight running sums of a four-row batch (x[2i] = dot_i, x[2i+1] = |b_i|^2) over the
+// warp and return this lane's row score: lane l ends up with row (l >> 3).  Transposed xor
+// butterfly: at offsets 16, 8, 4 each lane keeps half of its sums and ships the other half, then
+// two plain steps -- every addition pairs the same two operands as the plain butterfly would.
+__device__ __forceinline__ float reduce_batch_scores(const double (&x)[8], const double (&na_row)[4], int lane) {
+    double y4[4], y2[2], y1;
+    {
+        const bool hi = lane & 16;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const double keep = hi ? x[k + 4] : x[k], send = hi ? x[k] : x[k + 4];
+            y4[k] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
+        }
+    }
+    {
+        const bool hi = lane & 8;
+#pragma unroll
+        for (int k = 0; k < 2; ++k) {
+            const double keep = hi ? y4[k + 2] : y4[k], send = hi ? y4[k] : y4[k + 2];
+            y2[k] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
+        }
+    }
+    {
+        const bool hi = lane & 4;
+        const double keep = hi ? y2[1] : y2[0], send = hi ? y2[0] : y2[1];
+        y1 = keep + __shfl_xor_sync(0xffffffffu, send, 4);
+    }
+    y1 += __shfl_xor_sync(0xffffffffu, y1, 2);
+    y1 += __shfl_xor_sync(0xffffffffu, y1, 1);
+    // lane l now holds sum number (l >> 2) & 7 = 2 * row + kind, kind = (l >> 2) & 1 (0 dot, 1 |b|^2)
+    const double other = __shfl_xor_sync(0xffffffffu, y1, 4);
+    const bool is_nb = (lane >> 2) & 1;
+    const double dot = is_nb ? other : y1, nb = is_nb ? y1 : other;
+    const int my_i = lane >> 3;
+    const double my_na = my_i == 0 ? na_row[0] : my_i == 1 ? na_row[1] : my_i == 2 ? na_row[2] : na_row[3];
+    return score_from(dot, my_na, nb);
+}
+
+// FAST: D == NC * 128 (no partial chunk) and one user per stage -- the benchmark shape.
+template <int NC, bool FAST>
+__global__ void __launch_bounds__(TMA_THREADS, 1) cosine_tma_kernel(const CosTmaParams p) {
+    extern __shared__ __align__(128) unsigned char smem[];
+    uint64_t *full = reinterpret_cast<uint64_t *>(smem);                 // [stages]
+    uint64_t *empty = full + TMA_MAX_STAGES;                             // [stages]
+    unsigned int *s_hist = reinterpret_cast<unsigned int *>(smem + 128); // [2048]
+    unsigned char *ring = smem + 128 + FLR_SELECT_BINS * 4;
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const bool do_hist = p.hist0 != nullptr;
+    if (do_hist)
+        for (int i = tid; i < FLR_SELECT_BINS; i += TMA_THREADS) s_hist[i] = 0u;
+    if (tid == 0) {
+        for (int s = 0; s < p.stages; ++s) {
+            mbar_init(full + s, 1);
+            mbar_init(empty + s, TMA_CONSUMER_WARPS);
+        }
+        fence_mbar_init();
+    }
+    __syncthreads();
+
+    const int V = p.V, D = p.D, G = p.G;
+    const int nchunk = D >> 2;
+    const int64_t n_groups = (p.U + G - 1) / G;
+
+    if (warp == TMA_CONSUMER_WARPS) {
+        // ===== producer: one thread keeps the ring full =====
+        if (lane == 0) {
+            int s = 0;
+            uint32_t ph = 1;                                  // first pass over the ring never waits
+            for (int64_t g = blockIdx.x; g < n_groups; g += gridDim.x) {
+                mbar_wait(empty + s, ph);
+                const int64_t u0 = g * G;
+                const uint32_t nu = static_cast<uint32_t>(min(static_cast<int64_t>(G), p.U - u0));
+                const uint32_t ab = nu * D * 4u, bb = nu * V * D * 4u;
+                unsigned char *dst = ring + static_cast<size_t>(s) * p.stage_bytes;
+                mbar_expect_tx(full + s, ab + bb);
+                bulk_g2s_stream(dst, p.a + u0 * D, ab, full + s);
+                bulk_g2s_stream(dst + p.a_bytes, p.b + u0 * V * D, bb, full + s);
+                if (++s == p.stages) { s = 0; ph ^= 1u; }
+            }
+        }
+    } else {
+        // ===== consumers: batches of four rows =====
+        int s = 0;
+        uint32_t ph = 0;
+        int64_t it = 0;
+        for (int64_t g = blockIdx.x; g < n_groups; g += gridDim.x, ++it) {
+            mbar_wait(full + s, ph);
+            const int64_t u0 = g * G;
+            const float *sa = reinterpret_cast<const float *>(ring + static_cast<size_t>(s) * p.stage_bytes);
+            const float *sb = reinterpret_cast<const float *>(ring + static_cast<size_t>(s) * p.stage_bytes + p.a_bytes);
+            // rotate the batch -> warp map from stage to stage so short stages still use every warp
+            const int first = static_cast<int>((warp + TMA_CONSUMER_WARPS - (it % TMA_CONSUMER_WARPS)) % TMA_CONSUMER_WARPS);
+            double av[NC][4];
+            double na = 0.0;
+            if constexpr (FAST) {
+                const int rows = V;
+                const int n_batches = (rows + 3) >> 2;
+                {   // the stage's single anchor row, kept as fp64 for the whole stage
+                    double acc = 0.0;
+#pragma unroll
+                    for (int c = 0; c < NC; ++c) {
+                        const float4 q = *reinterpret_cast<const float4 *>(sa + 4 * (lane + 32 * c));
+                        av[c][0] = q.x; av[c][1] = q.y; av[c][2] = q.z; av[c][3] = q.w;
+#pragma unroll
+                        for (int e = 0; e < 4; ++e) acc = fma(av[c][e], av[c][e], acc);
+                    }
+                    na = warp_sum(acc);
+                }
+                for (int batch = first; batch < n_batches; batch += TMA_CONSUMER_WARPS) {
+                    const int r0 = batch * 4;
+                    double x[8];
+                    const double na_row[4] = {na, na, na, na};
+                    if (r0 + 4 <= rows) {                      // full batch: twelve independent 128-bit loads
+                        float4 q[4][NC];
+#pragma unroll
+                        for (int i = 0; i < 4; ++i)
+#pragma unroll
+                            for (int c = 0; c < NC; ++c)
+                                q[i][c] = *reinterpret_cast<const float4 *>(sb + static_cast<size_t>(r0 + i) * D + 4 * (lane + 32 * c));
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) {
+                            double d = 0.0, n = 0.0;
+#pragma unroll
+                            for (int c = 0; c < NC; ++c) fma4(av[c], q[i][c], d, n);
+                            x[2 * i] = d; x[2 * i + 1] = n;
+                        }
+                    } else {
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) {
+                            double d = 0.0, n = 0.0;
+                            if (r0 + i < rows) {
+#pragma unroll
+                                for (int c = 0; c < NC; ++c)
+                                    fma4(av[c], *reinterpret_cast<const float4 *>(sb + static_cast<size_t>(r0 + i) * D + 4 * (lane + 32 * c)), d, n);
+                            }
+                            x[2 * i] = d; x[2 * i + 1] = n;
+                        }
+                    }
+                    const float sc = reduce_batch_scores(x, na_row, lane);
+                    const int r = r0 + (lane >> 3);
+                    if ((lane & 7) == 0 && r < rows) {
+                        p.out[u0 * V + r] = sc;
+                        if (do_hist) atomicAdd(&s_hist[select_key::key_f32(sc) >> 21], 1u);
+                    }
+                }
+            } else {
+                const int nu = static_cast<int>(min(static_cast<int64_t>(G), p.U - u0));
+                const int rows = nu * V;
+                const int n_batches = (rows + 3) >> 2;
+                int cur_g = -1;
+                for (int batch = first; batch < n_batches; batch += TMA_CONSUMER_WARPS) {
+                    double x[8];
+                    double na_row[4];
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) {
+                        const int r = batch * 4 + i;
+                        x[2 * i] = 0.0; x[2 * i + 1] = 0.0;
+                        na_row[i] = 0.0;
+                        if (r < rows) {
+                            const int gi = r / V;
+                            if (gi != cur_g) {                     // warp-uniform
+                                load_row_f64<NC>(sa + static_cast<size_t>(gi) * D, lane, nchunk, av);
+                                double acc = 0.0;
+#pragma unroll
+                                for (int c = 0; c < NC; ++c)
+#pragma unroll
+                                    for (int e = 0; e < 4; ++e) acc = fma(av[c][e], av[c][e], acc);
+                                na = warp_sum(acc);
+                                cur_g = gi;
+                            }
+                            na_row[i] = na;
+                            const float *brow = sb + static_cast<size_t>(r) * D;
+                            double d = 0.0, n = 0.0;
+#pragma unroll
+                            for (int c = 0; c < NC; ++c) {
+                                const int ch = lane + 32 * c;
+                                float4 q = make_float4(0.f, 0.f, 0.f, 0.f);
+                                if (ch < nchunk) q = *reinterpret_cast<const float4 *>(brow + 4 * ch);
+                                fma4(av[c], q, d, n);
+                            }
+                            x[2 * i] = d; x[2 * i + 1] = n;
+                        }
+                    }
+                    const float sc = reduce_batch_scores(x, na_row, lane);
+                    const int r = batch * 4 + (lane >> 3);
+                    if ((lane & 7) == 0 && r < rows) {
+                        p.out[u0 * V + r] = sc;
+                        if (do_hist) atomicAdd(&s_hist[select_key::key_f32(sc) >> 21], 1u);
+                    }
+                }
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(empty + s);
+            if (++s == p.stages) { s = 0; ph ^= 1u; }
+        }
+    }
+    __syncthreads();
+    if (do_hist)
+        for (int i = tid; i < FLR_SELECT_BINS; i += TMA_THREADS) {
+            const unsigned int c = s_hist[i];
+            if (c) atomicAdd(p.hist0 + i, static_cast<unsigned long long>(c));
+        }
+}
+
+// Returns false when the shape does not suit the TMA kernel (caller falls back to the LDG kernel).
+template <int NC>
+bool launch_cos_tma(const float *a, const float *b, int64_t U, int V, int D, float *out, uint64_t *hist0,
+                    cudaStream_t stream, int *rc) {
+    const size_t user_bytes = static_cast<size_t>(V + 1) * D * 4;
+    const size_t budget = 200 * 1024;                        // ring bytes per SM
+    if (user_bytes * 2 > budget) return false;               // fewer than two stages would fit
+    int G = 1;
+    while ((G + 1) * user_bytes <= 50 * 1024 && (G * V) < 4 * TMA_CONSUMER_WARPS) ++G;
+    CosTmaParams p{};
+    p.a = a; p.b = b; p.U = U; p.V = V; p.D = D; p.G = G; p.out = out;
+    p.hist0 = reinterpret_cast<unsigned long long *>(hist0);
+    p.a_bytes = static_cast<uint32_t>((static_cast<size_t>(G) * D * 4 + 127) & ~static_cast<size_t>(127));
+    p.stage_bytes = static_cast<uint32_t>((p.a_bytes + static_cast<size_t>(G) * V * D * 4 + 127) & ~static_cast<size_t>(127));
+    p.stages = static_cast<int>(std::min<size_t>(TMA_MAX_STAGES, budget / p.stage_bytes));
+    if (p.stages < 2) return false;
+    const size_t smem = 128 + FLR_SELECT_BINS * 4 + static_cast<size_t>(p.stages) * p.stage_bytes;
+    const int64_t n_groups = (U + G - 1) / G;
+    const int grid = static_cast<int>(std::min<int64_t>(n_groups, device_sm_count()));
+    const bool fast = (G == 1) && (D == NC * 128);
+    auto kern = fast ? cosine_tma_kernel<NC, true> : cosine_tma_kernel<NC, false>;
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
+    if (e != cudaSuccess) {
+        set_error("cudaFuncSetAttribute(cosine_tma_kernel) failed: %s", cudaGetErrorString(e));
+        *rc = FLR_E_CUDA;
+        return true;
+    }
+    kern<<<grid, TMA_THREADS, smem, stream>>>(p);
+    e = cudaGetLastError();
+    if (e != cudaSuccess) {
+        set_error("launch of cosine_tma_kernel failed: %s", cudaGetErrorString(e));
+        *rc = FLR_E_CUDA;
+        return true;
+    }
+    *rc = FLR_OK;
+    return true;
+}
+
 template <int NC>
 int launch_cos(const float *a, const float *b, int64_t U, int V, int D, float *out, uint64_t *hist0,
                cudaStream_t stream) {
+    int rc = FLR_OK;
+    if (launch_cos_tma<NC>(a, b, U, V, D, out, hist0, stream, &rc)) return rc;
     const int sms = device_sm_count();
     const int64_t need = (U + COS_WARPS - 1) / COS_WARPS;
     const int grid = static_cast<int>(std::min<int64_t>(need, static_cast<int64_t>(sms) * 8));
