@@ -49,7 +49,7 @@ __host__ __device__ inline LmSmem lm_layout(int T, int V, int K, int vocab_pad, 
     s.off_nlen = o;    o = align16(o + static_cast<size_t>(T) * 4);
     s.off_na = o;      o = align16(o + static_cast<size_t>(T) * 4);
     s.off_tab = o;     o = align16(o + static_cast<size_t>(T) * vocab_pad);
-    s.off_bits = o;    o = align16(o + static_cast<size_t>(W) * NT * 4);
+    s.off_bits = o;    o = align16(o + static_cast<size_t>(W + 1) * NT * 4);   // +1: per-thread spare word
     s.total = o;
     return s;
 }
@@ -307,6 +307,7 @@ __global__ void __launch_bounds__(NT, 2) list_metrics_reg_kernel(const LmParams 
         const int n4 = T * p.vocab_pad / 16;
         for (int i = t; i < n4; i += NT) tab4[i] = make_int4(-1, -1, -1, -1);
         for (int w = 0; w < p.W; ++w) s_bits[w * NT + t] = 0u;
+        s_bits[p.W * NT + t] = 0xFFFFFFFFu;                   // spare word: "already seen" for non-elements
         if (t == 0) {
             mbar_init(bar, 1);
             fence_mbar_init();
@@ -413,44 +414,52 @@ __global__ void __launch_bounds__(NT, 2) list_metrics_reg_kernel(const LmParams 
         if (live) {
             const uint8_t *tab = s_tab + slot * p.vocab_pad;
             // phase A: all rank look-ups, independent of one another.  ids[j] is repacked as
-            //   bits 0-15  byte offset of the element's word in the private bit set ((id >> 5) * NT * 4)
-            //   bits 16-20 bit position (id & 31)      bits 21-28 rank in the neutral list (0xFF absent)
-            //   bit 31     element is not part of the row (padding, cut by k_cap, or out of vocabulary)
-            // An excluded element points at word 0 with an empty bit, so phase B needs no branch.
-        #pragma unroll
+            //   bits 0-15   index of the element's word in s_words (this thread's private bit set)
+            //   bits 16-21  rank in the neutral list, 63 when absent      bits 27-31  bit position (id & 31)
+            // An element that is not part of the row (padding, cut by k_cap, out of vocabulary) points
+            // at this thread's spare word, which is all ones: it always looks like a repeat.
+            static_assert(kTableSmemBudget / 4 <= 65536, "every shared-memory word index must fit 16 bits");
+            const uint32_t *s_words_c = reinterpret_cast<const uint32_t *>(smem);
+            uint32_t *s_words = reinterpret_cast<uint32_t *>(smem);
+            const unsigned word_base = static_cast<unsigned>(L.off_bits / 4) + t;       // word 0 of my bit set
+            const unsigned spare = word_base + static_cast<unsigned>(p.W) * NT;          // my all-ones word
+            int n_ok = 0;
+#pragma unroll
             for (int j = 0; j < KT; ++j) {
                 const unsigned id = ids[j];
-                const bool in_row = j < Kb;
-                const bool ok = in_row && id < vocab;
-                oov += (in_row && !ok) ? 1 : 0;
+                const bool ok = (j < Kb) && (id < vocab);
+                n_ok += ok ? 1 : 0;
                 const unsigned idc = ok ? id : 0u;
-                const unsigned r = tab[idc];
-                ids[j] = ((idc >> 5) * (NT * 4)) | ((idc & 31u) << 16) | (r << 21) | (ok ? 0u : 0x80000000u);
+                const unsigned rr = min(static_cast<unsigned>(tab[idc]), 63u);
+                const unsigned widx = ok ? (idc >> 5) * NT + word_base : spare;
+                ids[j] = widx | (rr << 16) | (idc << 27);
             }
-            // phase B: duplicate test through the private bit set + metric updates, branch-free
-            const char *bits_base = reinterpret_cast<const char *>(s_bits + t);
-            uint64_t seen2 = 0;                      // (mask of neutral ranks already hit) << 1
-            int n_b = 0, inter = 0, serp = 0, prag = 0;
+            oov += Kb - n_ok;
+            // phase B: duplicate test through the private bit set + metric updates, branch-free.
+            // seen2 = (mask of neutral ranks already hit) << 1.  For an absent item rr = 63, so
+            // "hits ranked below it" counts every hit so far and 2 << 63 adds no bit.
+            uint64_t seen2 = 0;
+            int n_b = 0, pos_sum = 0, prag = 0;
 #pragma unroll
             for (int j = 0; j < KT; ++j) {
                 const unsigned x = ids[j];
-                uint32_t *wp = reinterpret_cast<uint32_t *>(const_cast<char *>(bits_base) + (x & 0xFFFFu));
-                const uint32_t w = *wp;
-                const uint32_t b = (x >> 31) ? 0u : (1u << ((x >> 16) & 31u));
-                *wp = w | b;
-                const bool first = (b & ~w) != 0u;                       // a live element whose bit was clear
-                const unsigned r = (x >> 21) & 0xFFu;
-                const bool hit = first && r != 0xFFu;
-                n_b += first ? 1 : 0;
+                const unsigned wi = x & 0xFFFFu;
+                const uint32_t w = s_words_c[wi];
+                const uint32_t bit = 1u << (x >> 27);
+                s_words[wi] = w | bit;
+                const bool first = (w & bit) == 0u;
+                const unsigned rr = (x >> 16) & 63u;
+                if (first) ++n_b;
                 if constexpr (RANK) {
-                    const unsigned rr = r & 63u;
-                    const int below = __popcll(seen2 << (63u - rr));     // earlier hits with a smaller rank
-                    prag += hit ? below : (first ? inter : 0);            // absent item: every earlier hit counts
-                    serp += hit ? (Kn - j) : 0;
-                    seen2 |= hit ? (2ull << rr) : 0ull;
+                    const int below = __popcll(seen2 << (rr ^ 63u));
+                    if (first) prag += below;
+                    if (first && rr != 63u) pos_sum += j;
                 }
-                inter += hit ? 1 : 0;
+                const uint64_t add = static_cast<uint64_t>(first ? 2u : 0u) << rr;
+                seen2 |= add;
             }
+            const int inter = __popcll(seen2);
+            const int serp = inter * Kn - pos_sum;              // sum over hits of (Kn - j)
             const int n_a = s_na[slot];
             const int uni = n_a + n_b - inter;
             double jac;
@@ -470,10 +479,10 @@ __global__ void __launch_bounds__(NT, 2) list_metrics_reg_kernel(const LmParams 
             acc_s += serp;
             acc_p += prag;
             acc_n += 1;
-            // wipe the private bit set (word offsets are still in registers)
+            // wipe the private bit set (word indices are still in registers), re-arm the spare word
 #pragma unroll
-            for (int j = 0; j < KT; ++j)
-                *reinterpret_cast<uint32_t *>(const_cast<char *>(bits_base) + (ids[j] & 0xFFFFu)) = 0u;
+            for (int j = 0; j < KT; ++j) s_words[ids[j] & 0xFFFFu] = 0u;
+            s_words[spare] = 0xFFFFFFFFu;
         }
         __syncthreads();
 
