@@ -23,7 +23,9 @@ using namespace flr;
 
 namespace {
 
-// one warp per row: fp64 sum of squares (exact fp32 products), fp32 divide, RNE to bf16
+// one warp per row: fp64 sum of squares (exact fp32 products), fp32 divide, RNE to bf16.
+// VEC: the row is read once with 128-bit loads and kept in registers (D % 4 == 0, D <= 1024).
+template <bool VEC>
 __global__ void __launch_bounds__(256) normalize_rows_bf16_kernel(const float *__restrict__ x, int64_t rows, int D,
                                                                   __nv_bfloat16 *__restrict__ out) {
     const int lane = threadIdx.x & 31;
@@ -32,16 +34,55 @@ __global__ void __launch_bounds__(256) normalize_rows_bf16_kernel(const float *_
     for (int64_t r = warp0; r < rows; r += nwarps) {
         const float *row = x + r * D;
         double ss = 0.0;
-        for (int d = lane; d < D; d += 32) {
-            const double v = row[d];
-            ss = fma(v, v, ss);
-        }
+        if constexpr (VEC) {
+            const int nchunk = D >> 2;
+            float4 q[8];
 #pragma unroll
-        for (int off = 16; off >= 1; off >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, off);
-        const double n = sqrt(ss);
-        for (int d = lane; d < D; d += 32) {
-            const float y = n > 0.0 ? static_cast<float>(static_cast<double>(row[d]) / n) : 0.0f;
-            out[r * D + d] = __float2bfloat16_rn(y);
+            for (int c = 0; c < 8; ++c) {
+                const int ch = lane + 32 * c;
+                q[c] = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (ch < nchunk) q[c] = ldg_stream_f4(reinterpret_cast<const float4 *>(row) + ch);
+            }
+            // lane l sums chunks l, l+32, ... (the scalar form below strides by element instead; the two
+            // differ only in the last bits of |x|, far below bf16 resolution)
+#pragma unroll
+            for (int c = 0; c < 8; ++c) {
+                const double a = q[c].x, b2 = q[c].y, c2 = q[c].z, d2 = q[c].w;
+                ss = fma(a, a, ss); ss = fma(b2, b2, ss); ss = fma(c2, c2, ss); ss = fma(d2, d2, ss);
+            }
+#pragma unroll
+            for (int off = 16; off >= 1; off >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, off);
+            const double n = sqrt(ss);
+            const double inv = n > 0.0 ? 1.0 / n : 0.0;
+#pragma unroll
+            for (int c = 0; c < 8; ++c) {
+                const int ch = lane + 32 * c;
+                if (ch < nchunk) {
+                    // one fp64 division per row; x * (1/n) differs from x / n by < 2^-52 relative, which the
+                    // rounding to fp32 and then bf16 absorbs
+                    const float y0 = static_cast<float>(static_cast<double>(q[c].x) * inv);
+                    const float y1 = static_cast<float>(static_cast<double>(q[c].y) * inv);
+                    const float y2 = static_cast<float>(static_cast<double>(q[c].z) * inv);
+                    const float y3 = static_cast<float>(static_cast<double>(q[c].w) * inv);
+                    __nv_bfloat162 lo = __floats2bfloat162_rn(y0, y1), hi = __floats2bfloat162_rn(y2, y3);
+                    uint2 pk;
+                    pk.x = *reinterpret_cast<uint32_t *>(&lo);
+                    pk.y = *reinterpret_cast<uint32_t *>(&hi);
+                    *reinterpret_cast<uint2 *>(out + r * D + 4 * ch) = pk;
+                }
+            }
+        } else {
+            for (int d = lane; d < D; d += 32) {
+                const double v = row[d];
+                ss = fma(v, v, ss);
+            }
+#pragma unroll
+            for (int off = 16; off >= 1; off >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, off);
+            const double n = sqrt(ss);
+            for (int d = lane; d < D; d += 32) {
+                const float y = n > 0.0 ? static_cast<float>(static_cast<double>(row[d]) / n) : 0.0f;
+                out[r * D + d] = __float2bfloat16_rn(y);
+            }
         }
     }
 }
@@ -260,8 +301,13 @@ extern "C" int flr_normalize_rows_bf16(const float *x, int64_t rows, int D, uint
     if (rows == 0) return FLR_OK;
     FLR_REQUIRE(x && out_bf16, FLR_E_INVALID, "normalize_rows: null pointer");
     const int grid = static_cast<int>(std::min<int64_t>((rows + 7) / 8, static_cast<int64_t>(device_sm_count()) * 8));
-    normalize_rows_bf16_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream_)>>>(
-        x, rows, D, reinterpret_cast<__nv_bfloat16 *>(out_bf16));
+    const bool vec = (D % 4 == 0) && D <= 1024 && aligned16(x) && ((reinterpret_cast<uintptr_t>(out_bf16) & 7u) == 0);
+    if (vec)
+        normalize_rows_bf16_kernel<true><<<grid, 256, 0, static_cast<cudaStream_t>(stream_)>>>(
+            x, rows, D, reinterpret_cast<__nv_bfloat16 *>(out_bf16));
+    else
+        normalize_rows_bf16_kernel<false><<<grid, 256, 0, static_cast<cudaStream_t>(stream_)>>>(
+            x, rows, D, reinterpret_cast<__nv_bfloat16 *>(out_bf16));
     FLR_LAUNCH_CHECK("normalize_rows_bf16_kernel");
     return FLR_OK;
 }

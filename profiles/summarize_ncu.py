@@ -1,5 +1,5 @@
 """Summarise an ncu report (read here, on the CPU box):
-    python profiles/summarize_ncu.py gpurun_out/prof.ncu-rep profiles/rNN_name
+    python profiles/summarize_ncu.py gpurun_out/prof.ncu-rep profiles/rNN_name <pairs per launch> [note]
 writes <out>_summary.csv (one row per captured launch, the metrics the roofline argument uses)
 and updates profiles/traffic.json (per-kernel DRAM bytes per launch, scaled note included)."""
 import csv, json, os, subprocess, sys
@@ -31,14 +31,19 @@ def main():
     traffic = {}
     for r in data:
         name = r[idx["Kernel Name"]]
-        short = "cosine_kernel" if "cosine_kernel" in name else "list_metrics_table_kernel" if "list_metrics_table" in name else name
+        short = ("cosine_kernel" if "cosine" in name else
+                 "list_metrics_table_kernel" if ("list_metrics_table" in name or "list_metrics_reg" in name) else name)
         b = (to_bytes(r[idx["dram__bytes_read.sum"]], units[idx["dram__bytes_read.sum"]]) +
              to_bytes(r[idx["dram__bytes_write.sum"]], units[idx["dram__bytes_write.sum"]]))
         traffic.setdefault(short, []).append(b)
     tj = os.path.join(os.path.dirname(os.path.abspath(__file__)), "traffic.json")
-    note = sys.argv[3] if len(sys.argv) > 3 else ""
-    json.dump({"source": os.path.basename(out), "note": note,
-               "dram_bytes_per_launch": {k: sum(v) / len(v) for k, v in traffic.items()}}, open(tj, "w"), indent=1)
+    pairs = float(sys.argv[3]) if len(sys.argv) > 3 else None      # (user, variant) pairs per captured launch
+    note = sys.argv[4] if len(sys.argv) > 4 else ""
+    per_launch = {k: sum(v) / len(v) for k, v in traffic.items()}
+    json.dump({"source": os.path.basename(out), "note": note, "pairs_per_captured_launch": pairs,
+               "dram_bytes_per_launch": per_launch,
+               "dram_bytes_per_pair": {k: v / pairs for k, v in per_launch.items()} if pairs else None},
+              open(tj, "w"), indent=1)
     print(open(out + "_summary.csv").read())
 
 if __name__ == "__main__":
