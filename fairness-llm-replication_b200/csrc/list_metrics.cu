@@ -293,7 +293,7 @@ __global__ void __launch_bounds__(NT, 2) list_metrics_reg_kernel(const LmParams 
     int32_t *s_keep_len = s_keep + p.T * KT;                                  // [T]
 
     constexpr int VEC = (KT % 4 == 0) ? 4 : 2;
-    static_assert(KT % 2 == 0 && KT <= 64, "row length must be even and fit the rank mask");
+    static_assert(KT % 2 == 0 && KT <= 62, "row length must be even; rank 63 is the absent marker");
 
     const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
     const int V = p.V, T = p.T, Kn = p.k_cap;
@@ -305,9 +305,9 @@ __global__ void __launch_bounds__(NT, 2) list_metrics_reg_kernel(const LmParams 
     {
         int4 *tab4 = reinterpret_cast<int4 *>(s_tab);
         const int n4 = T * p.vocab_pad / 16;
-        for (int i = t; i < n4; i += NT) tab4[i] = make_int4(-1, -1, -1, -1);
+        for (int i = t; i < n4; i += NT) tab4[i] = make_int4(0x3F3F3F3F, 0x3F3F3F3F, 0x3F3F3F3F, 0x3F3F3F3F);   // 63 = absent
         for (int w = 0; w < p.W; ++w) s_bits[w * NT + t] = 0u;
-        s_bits[p.W * NT + t] = 0xFFFFFFFFu;                   // spare word: "already seen" for non-elements
+        s_bits[(vocab >> 5) * NT + t] = 1u << (vocab & 31u);  // the spare element `vocab` is always "seen before"
         if (t == 0) {
             mbar_init(bar, 1);
             fence_mbar_init();
@@ -353,7 +353,7 @@ __global__ void __launch_bounds__(NT, 2) list_metrics_reg_kernel(const LmParams 
 
         // ---- move the tile out of the stage buffer: own row -> registers, neutral lists -> s_keep ----
         unsigned ids[KT];
-        int Kb = 0;
+        int Kb = KT;
         const bool live = pair_thread && slot < tu;
         if (live) {
             Kb = max(0, min(s_lens[t], Kn));
@@ -365,6 +365,13 @@ __global__ void __launch_bounds__(NT, 2) list_metrics_reg_kernel(const LmParams 
 #pragma unroll
                 for (int e = 0; e < VEC; ++e) ids[j0 + e] = static_cast<unsigned>(tmp[e]);
             }
+        }
+        // Rows shorter than KT are rare: only a warp that holds one pays for masking the tail.  A
+        // masked position holds the id `vocab`, the spare element (see the main loop).
+        if (__any_sync(0xffffffffu, Kb < KT)) {
+#pragma unroll
+            for (int j = 0; j < KT; ++j)
+                if (j >= Kb) ids[j] = vocab;
         }
         for (int i = t; i < tu * KT; i += NT) s_keep[i] = s_neutral[i];
         for (int i = t; i < tu; i += NT) s_keep_len[i] = max(0, min(s_nlen[i], Kn));
@@ -413,53 +420,55 @@ __global__ void __launch_bounds__(NT, 2) list_metrics_reg_kernel(const LmParams 
 
         if (live) {
             const uint8_t *tab = s_tab + slot * p.vocab_pad;
-            // phase A: all rank look-ups, independent of one another.  ids[j] is repacked as
-            //   bits 0-15   index of the element's word in s_words (this thread's private bit set)
-            //   bits 16-21  rank in the neutral list, 63 when absent      bits 27-31  bit position (id & 31)
-            // An element that is not part of the row (padding, cut by k_cap, out of vocabulary) points
-            // at this thread's spare word, which is all ones: it always looks like a repeat.
-            static_assert(kTableSmemBudget / 4 <= 65536, "every shared-memory word index must fit 16 bits");
-            const uint32_t *s_words_c = reinterpret_cast<const uint32_t *>(smem);
-            uint32_t *s_words = reinterpret_cast<uint32_t *>(smem);
-            const unsigned word_base = static_cast<unsigned>(L.off_bits / 4) + t;       // word 0 of my bit set
-            const unsigned spare = word_base + static_cast<unsigned>(p.W) * NT;          // my all-ones word
-            int n_ok = 0;
+            // One fused, branch-free pass over the row (fully unrolled, so the compiler hoists the
+            // independent rank look-ups ahead of the bit set's load -> store chain).
+            //   * The id `vocab` is a spare element: its bit in this thread's set is always 1 ("seen
+            //     before") and its table entry always reads "absent".  min(id, vocab) sends padding
+            //     (-1 or anything >= vocab as unsigned), masked tail positions and out-of-vocabulary ids
+            //     there, so they contribute nothing and need no test.
+            //   * An absent item has rank 63: "hits ranked below it" then counts every hit so far, and
+            //     2 << 63 adds no bit, so the rank mask update needs no condition (a repeated present
+            //     item sets a bit that is already set).
+            // seen2 = (mask of neutral ranks already hit) << 1; hitpos = positions of the hits.
+            char *bits_base = reinterpret_cast<char *>(s_bits + t);
+            uint64_t seen2 = 0, hitpos = 0;
+            int n_b = 0, prag = 0;
 #pragma unroll
             for (int j = 0; j < KT; ++j) {
-                const unsigned id = ids[j];
-                const bool ok = (j < Kb) && (id < vocab);
-                n_ok += ok ? 1 : 0;
-                const unsigned idc = ok ? id : 0u;
-                const unsigned rr = min(static_cast<unsigned>(tab[idc]), 63u);
-                const unsigned widx = ok ? (idc >> 5) * NT + word_base : spare;
-                ids[j] = widx | (rr << 16) | (idc << 27);
-            }
-            oov += Kb - n_ok;
-            // phase B: duplicate test through the private bit set + metric updates, branch-free.
-            // seen2 = (mask of neutral ranks already hit) << 1.  For an absent item rr = 63, so
-            // "hits ranked below it" counts every hit so far and 2 << 63 adds no bit.
-            uint64_t seen2 = 0;
-            int n_b = 0, pos_sum = 0, prag = 0;
-#pragma unroll
-            for (int j = 0; j < KT; ++j) {
-                const unsigned x = ids[j];
-                const unsigned wi = x & 0xFFFFu;
-                const uint32_t w = s_words_c[wi];
-                const uint32_t bit = 1u << (x >> 27);
-                s_words[wi] = w | bit;
+                const unsigned idx = min(ids[j], vocab);
+                uint32_t *wp = reinterpret_cast<uint32_t *>(bits_base + (idx >> 5) * (NT * 4));
+                const uint32_t w = *wp;
+                const uint32_t bit = 1u << (idx & 31u);
+                *wp = w | bit;
                 const bool first = (w & bit) == 0u;
-                const unsigned rr = (x >> 16) & 63u;
                 if (first) ++n_b;
+                const unsigned rr = tab[idx];                  // 63 when absent
                 if constexpr (RANK) {
                     const int below = __popcll(seen2 << (rr ^ 63u));
                     if (first) prag += below;
-                    if (first && rr != 63u) pos_sum += j;
+                    if (first && rr != 63u) hitpos |= 1ull << j;
                 }
-                const uint64_t add = static_cast<uint64_t>(first ? 2u : 0u) << rr;
-                seen2 |= add;
+                seen2 |= 2ull << rr;
             }
             const int inter = __popcll(seen2);
-            const int serp = inter * Kn - pos_sum;              // sum over hits of (Kn - j)
+            int serp = 0;
+            if constexpr (RANK) {       // sum over hits of (Kn - j), from the position mask
+                const uint32_t lo = static_cast<uint32_t>(hitpos), hi = static_cast<uint32_t>(hitpos >> 32);
+                int pos_sum = 32 * __popc(hi);
+#pragma unroll
+                for (int bshift = 0; bshift < 5; ++bshift) {
+                    const uint32_t m = bshift == 0 ? 0xAAAAAAAAu : bshift == 1 ? 0xCCCCCCCCu : bshift == 2 ? 0xF0F0F0F0u
+                                     : bshift == 3 ? 0xFF00FF00u : 0xFFFF0000u;
+                    pos_sum += (__popc(lo & m) + __popc(hi & m)) << bshift;
+                }
+                serp = inter * Kn - pos_sum;
+            }
+            if (n_b != Kb) {            // repeats or foreign ids in this row (rare): count the foreign ids
+                int spare_hits = 0;
+#pragma unroll
+                for (int j = 0; j < KT; ++j) spare_hits += ids[j] >= vocab ? 1 : 0;
+                oov += spare_hits - (KT - Kb);
+            }
             const int n_a = s_na[slot];
             const int uni = n_a + n_b - inter;
             double jac;
@@ -479,10 +488,12 @@ __global__ void __launch_bounds__(NT, 2) list_metrics_reg_kernel(const LmParams 
             acc_s += serp;
             acc_p += prag;
             acc_n += 1;
-            // wipe the private bit set (word indices are still in registers), re-arm the spare word
-#pragma unroll
-            for (int j = 0; j < KT; ++j) s_words[ids[j] & 0xFFFFu] = 0u;
-            s_words[spare] = 0xFFFFFFFFu;
+            // wipe the private bit set and re-arm the spare element's bit
+            uint32_t *mybits = s_bits + t;
+            const int n_words = static_cast<int>(vocab >> 5) + 1;
+#pragma unroll 8
+            for (int w = 0; w < n_words; ++w) mybits[w * NT] = 0u;
+            mybits[(vocab >> 5) * NT] = 1u << (vocab & 31u);
         }
         __syncthreads();
 
@@ -492,7 +503,7 @@ __global__ void __launch_bounds__(NT, 2) list_metrics_reg_kernel(const LmParams 
             uint8_t *tab = s_tab + s * p.vocab_pad;
             for (int j = lane; j < Ka; j += 32) {
                 const unsigned id = static_cast<unsigned>(A[j]);
-                if (id < vocab) tab[id] = 0xFFu;
+                if (id < vocab) tab[id] = 63u;
             }
         }
         __syncthreads();
@@ -639,7 +650,7 @@ struct Plan {
 Plan make_plan(int64_t U, int V, int K, int k_cap, int vocab) {
     Plan pl{};
     const int sms = device_sm_count();
-    pl.vocab_pad = (vocab + 15) & ~15;
+    pl.vocab_pad = (vocab + 16) & ~15;       // > vocab: entry [vocab] is a spare that always reads "absent"
     pl.W = (vocab + 31) / 32;
     pl.table = false;
     if (vocab > 0 && vocab <= 16384 && k_cap <= FLR_MAX_RANK_K && V >= 2 && V <= NT) {
