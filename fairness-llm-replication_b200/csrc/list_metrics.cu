@@ -291,6 +291,7 @@ __global__ void __launch_bounds__(NT, 2) list_metrics_reg_kernel(const LmParams 
     uint32_t *s_bits = reinterpret_cast<uint32_t *>(smem + L.off_bits);
     int32_t *s_keep = reinterpret_cast<int32_t *>(smem + L.total);          // [T][KT] neutral ids of the live tile
     int32_t *s_keep_len = s_keep + p.T * KT;                                  // [T]
+    double *s_recip = reinterpret_cast<double *>(smem + L.total + align16(static_cast<size_t>(p.T) * (KT * 4 + 4)));  // [2 KT + 1]
 
     constexpr int VEC = (KT % 4 == 0) ? 4 : 2;
     static_assert(KT % 2 == 0 && KT <= 62, "row length must be even; rank 63 is the absent marker");
@@ -308,6 +309,7 @@ __global__ void __launch_bounds__(NT, 2) list_metrics_reg_kernel(const LmParams 
         for (int i = t; i < n4; i += NT) tab4[i] = make_int4(0x3F3F3F3F, 0x3F3F3F3F, 0x3F3F3F3F, 0x3F3F3F3F);   // 63 = absent
         for (int w = 0; w < p.W; ++w) s_bits[w * NT + t] = 0u;
         s_bits[(vocab >> 5) * NT + t] = 1u << (vocab & 31u);  // the spare element `vocab` is always "seen before"
+        for (int i = t; i <= 2 * KT; i += NT) s_recip[i] = i > 0 ? 1.0 / static_cast<double>(i) : 0.0;
         if (t == 0) {
             mbar_init(bar, 1);
             fence_mbar_init();
@@ -329,6 +331,7 @@ __global__ void __launch_bounds__(NT, 2) list_metrics_reg_kernel(const LmParams 
     };
     auto tile_is_bulk = [&](int64_t tile) { return p.use_bulk && tile < n_tiles && (tile + 1) * T <= p.U; };
 
+    const float inv_serp = 1.0f / static_cast<float>(Kn * (Kn + 1) / 2), inv_prag = 1.0f / static_cast<float>(Kn * (Kn + 1));
     uint32_t phase = 0;
     double acc_j = 0.0;
     long long acc_s = 0, acc_p = 0;
@@ -378,42 +381,30 @@ __global__ void __launch_bounds__(NT, 2) list_metrics_reg_kernel(const LmParams 
         __syncthreads();
         if (t == 0 && tile_is_bulk(tile + gridDim.x)) issue_tma(tile + gridDim.x);   // overlaps everything below
 
-        // ---- rank tables ----
+        // ---- rank tables: tab[id] = first position of id in the neutral list (63 = absent) ----
         for (int s = warp; s < tu; s += NT / 32) {
             const int Ka = s_keep_len[s];
             const int32_t *A = s_keep + s * KT;
             uint8_t *tab = s_tab + s * p.vocab_pad;
-            for (int base = ((Ka - 1) >> 5) << 5; base >= 0; base -= 32) {
-                const int j = base + lane;
-                if (j < Ka) {
-                    const unsigned id = static_cast<unsigned>(A[j]);
-                    if (id < vocab) tab[id] = static_cast<uint8_t>(j); else ++oov;
-                }
-                __syncwarp();
-            }
+            const unsigned id0 = lane < Ka ? static_cast<unsigned>(A[lane]) : vocab;
+            const unsigned id1 = lane + 32 < Ka ? static_cast<unsigned>(A[lane + 32]) : vocab;
+            oov += (lane < Ka && id0 >= vocab ? 1 : 0) + (lane + 32 < Ka && id1 >= vocab ? 1 : 0);
+            if (id1 < vocab) tab[id1] = static_cast<uint8_t>(lane + 32);         // later half first,
+            __syncwarp();
+            if (id0 < vocab) tab[id0] = static_cast<uint8_t>(lane);              // so the earlier half wins
+            __syncwarp();
+            int cnt;
             bool again;
-            do {
+            do {    // repeats inside one 32-wide store raced: let the smallest position win, then count
+                const unsigned v0 = id0 < vocab ? tab[id0] : 0u, v1 = id1 < vocab ? tab[id1] : 0u;
                 again = false;
-                for (int base = 0; base < Ka; base += 32) {
-                    const int j = base + lane;
-                    if (j < Ka) {
-                        const unsigned id = static_cast<unsigned>(A[j]);
-                        if (id < vocab && tab[id] > j) { tab[id] = static_cast<uint8_t>(j); again = true; }
-                    }
-                }
-                __syncwarp();
+                if (id0 < vocab && v0 > static_cast<unsigned>(lane)) { tab[id0] = static_cast<uint8_t>(lane); again = true; }
+                if (id1 < vocab && v1 > static_cast<unsigned>(lane + 32)) { tab[id1] = static_cast<uint8_t>(lane + 32); again = true; }
+                cnt = __popc(__ballot_sync(0xffffffffu, id0 < vocab && v0 == static_cast<unsigned>(lane))) +
+                      __popc(__ballot_sync(0xffffffffu, id1 < vocab && v1 == static_cast<unsigned>(lane + 32)));
                 again = __any_sync(0xffffffffu, again);
+                __syncwarp();
             } while (again);
-            int cnt = 0;
-            for (int base = 0; base < Ka; base += 32) {
-                const int j = base + lane;
-                bool first = false;
-                if (j < Ka) {
-                    const unsigned id = static_cast<unsigned>(A[j]);
-                    first = id < vocab && tab[id] == j;
-                }
-                cnt += __popc(__ballot_sync(0xffffffffu, first));
-            }
             if (lane == 0) s_na[s] = cnt;
         }
         __syncthreads();
@@ -471,32 +462,38 @@ __global__ void __launch_bounds__(NT, 2) list_metrics_reg_kernel(const LmParams 
             }
             const int n_a = s_na[slot];
             const int uni = n_a + n_b - inter;
-            double jac;
-            if (p.empty_policy == FLR_EMPTY_BOTH_IS_ONE)
-                jac = uni > 0 ? static_cast<double>(inter) / static_cast<double>(uni) : 1.0;
-            else
-                jac = (n_a == 0 || n_b == 0) ? 0.0 : static_cast<double>(inter) / static_cast<double>(uni);
+            // inter * (1/uni) from a table instead of an fp64 division per pair: within one ulp of the
+            // quotient, which the fp32 output and the 1e-12 tolerance on the sums never see
+            double jac = static_cast<double>(inter) * s_recip[uni];
+            if (p.empty_policy == FLR_EMPTY_BOTH_IS_ONE) jac = uni > 0 ? jac : 1.0;
             const int64_t pair = u0 * V + t;
             if (p.out_inter) p.out_inter[pair] = inter;
             if (p.out_union) p.out_union[pair] = uni;
             if (p.out_jac) p.out_jac[pair] = static_cast<float>(jac);
             if constexpr (RANK) {
-                if (p.out_serp) p.out_serp[pair] = static_cast<float>(serp) / static_cast<float>(Kn * (Kn + 1) / 2);
-                if (p.out_prag) p.out_prag[pair] = static_cast<float>(prag) / static_cast<float>(Kn * (Kn + 1));
+                if (p.out_serp) p.out_serp[pair] = static_cast<float>(serp) * inv_serp;
+                if (p.out_prag) p.out_prag[pair] = static_cast<float>(prag) * inv_prag;
             }
             acc_j += jac;
             acc_s += serp;
             acc_p += prag;
             acc_n += 1;
-            // wipe the private bit set and re-arm the spare element's bit
-            uint32_t *mybits = s_bits + t;
-            const int n_words = static_cast<int>(vocab >> 5) + 1;
-#pragma unroll 8
-            for (int w = 0; w < n_words; ++w) mybits[w * NT] = 0u;
-            mybits[(vocab >> 5) * NT] = 1u << (vocab & 31u);
         }
         __syncthreads();
 
+        // ---- wipe every private bit set with 128-bit stores (the row of the spare element is
+        //      re-armed in the same sweep), and un-mark the rank tables ----
+        {
+            int4 *bits4 = reinterpret_cast<int4 *>(s_bits);
+            const int spare_row = static_cast<int>(vocab >> 5);
+            const int spare_val = static_cast<int>(1u << (vocab & 31u));
+            const int n4 = (spare_row + 1) * (NT / 4);
+#pragma unroll 4
+            for (int i = t; i < n4; i += NT) {
+                const int v = (i / (NT / 4) == spare_row) ? spare_val : 0;
+                bits4[i] = make_int4(v, v, v, v);
+            }
+        }
         for (int s = warp; s < tu; s += NT / 32) {
             const int Ka = s_keep_len[s];
             const int32_t *A = s_keep + s * KT;
@@ -655,8 +652,11 @@ Plan make_plan(int64_t U, int V, int K, int k_cap, int vocab) {
     pl.table = false;
     if (vocab > 0 && vocab <= 16384 && k_cap <= FLR_MAX_RANK_K && V >= 2 && V <= NT) {
         const bool reg = (K == 10 || K == 20 || K == 50);
-        const size_t extra = reg ? align16(static_cast<size_t>(1) * K * 4 + 4) : 0;     // per user slot
-        auto bytes = [&](int T) { return lm_layout(T, V, K, pl.vocab_pad, pl.W).total + (reg ? align16(extra * T) : 0); };
+        // register kernel extras: neutral ids + lengths of the live tile, and the reciprocal table
+        auto bytes = [&](int T) {
+            return lm_layout(T, V, K, pl.vocab_pad, pl.W).total +
+                   (reg ? align16(static_cast<size_t>(T) * (K * 4 + 4)) + align16((2 * K + 1) * sizeof(double)) : 0);
+        };
         int T = NT / V;
         if (T >= 4) T &= ~3;                 // multiples of 4 keep every bulk copy 16-byte sized
         while (T >= 1 && bytes(T) > static_cast<size_t>(kTableSmemBudget))
