@@ -376,18 +376,17 @@ __global__ void __launch_bounds__(NT, 2) list_metrics_reg_kernel(const LmParams 
             for (int j = 0; j < KT; ++j)
                 if (j >= Kb) ids[j] = vocab;
         }
-        for (int i = t; i < tu * KT; i += NT) s_keep[i] = s_neutral[i];
-        for (int i = t; i < tu; i += NT) s_keep_len[i] = max(0, min(s_nlen[i], Kn));
-        __syncthreads();
-        if (t == 0 && tile_is_bulk(tile + gridDim.x)) issue_tma(tile + gridDim.x);   // overlaps everything below
-
-        // ---- rank tables: tab[id] = first position of id in the neutral list (63 = absent) ----
+        // ---- rank tables: tab[id] = first position of id in the neutral list (63 = absent).  Slot s is
+        //      always handled by warp s % 4 -- build here, un-mark at the end of the tile -- so the two
+        //      need no barrier between them; the ids are parked in s_keep for the un-mark. ----
         for (int s = warp; s < tu; s += NT / 32) {
-            const int Ka = s_keep_len[s];
-            const int32_t *A = s_keep + s * KT;
+            const int Ka = max(0, min(s_nlen[s], Kn));
+            const int32_t *A = s_neutral + s * KT;
             uint8_t *tab = s_tab + s * p.vocab_pad;
             const unsigned id0 = lane < Ka ? static_cast<unsigned>(A[lane]) : vocab;
             const unsigned id1 = lane + 32 < Ka ? static_cast<unsigned>(A[lane + 32]) : vocab;
+            if (lane < KT) s_keep[s * KT + lane] = static_cast<int32_t>(id0);
+            if (lane + 32 < KT) s_keep[s * KT + lane + 32] = static_cast<int32_t>(id1);
             oov += (lane < Ka && id0 >= vocab ? 1 : 0) + (lane + 32 < Ka && id1 >= vocab ? 1 : 0);
             if (id1 < vocab) tab[id1] = static_cast<uint8_t>(lane + 32);         // later half first,
             __syncwarp();
@@ -407,7 +406,8 @@ __global__ void __launch_bounds__(NT, 2) list_metrics_reg_kernel(const LmParams 
             } while (again);
             if (lane == 0) s_na[s] = cnt;
         }
-        __syncthreads();
+        __syncthreads();       // stage buffer fully consumed, every table built
+        if (t == 0 && tile_is_bulk(tile + gridDim.x)) issue_tma(tile + gridDim.x);   // overlaps everything below
 
         if (live) {
             const uint8_t *tab = s_tab + slot * p.vocab_pad;
@@ -495,15 +495,16 @@ __global__ void __launch_bounds__(NT, 2) list_metrics_reg_kernel(const LmParams 
             }
         }
         for (int s = warp; s < tu; s += NT / 32) {
-            const int Ka = s_keep_len[s];
             const int32_t *A = s_keep + s * KT;
             uint8_t *tab = s_tab + s * p.vocab_pad;
-            for (int j = lane; j < Ka; j += 32) {
+            for (int j = lane; j < KT; j += 32) {
                 const unsigned id = static_cast<unsigned>(A[j]);
                 if (id < vocab) tab[id] = 63u;
             }
+            __syncwarp();      // every lane's un-mark lands before any lane of this warp re-marks the table
         }
-        __syncthreads();
+        // no barrier here: the next tile's first barrier orders this wipe before its main loop, and
+        // each table is rebuilt by the warp that just un-marked it
     }
 
     double *dst = p.partial + (static_cast<size_t>(blockIdx.x) * NT + t) * 4;
