@@ -1,0 +1,165 @@
+// Demographic parity: per-group item histograms and the pairwise
+// Jensen-Shannon distances between them -- utils.calculate_demographic_parity /
+// calculate_js_divergence, src/utils.py:172-215 and :89-102.
+//
+// group_item_histogram_kernel: one CTA per (group, slice of rows).  The CTA keeps the group's
+// `vocab` counters in shared memory; lanes that hold the same item in the same step are merged
+// with __match_any_sync before the shared-memory atomic (recommendation lists are Zipf-skewed:
+// most of a warp often holds the same few titles), then non-zero counters go to the global
+// uint64 histogram.  Every occurrence counts (no de-duplication, as in the reference).
+//
+// js_distance_kernel: one CTA per group pair (i < j).  Keys = items either group holds; a missing
+// key counts 1e-10; both sides are renormalised, then normalised once more exactly as
+// scipy.spatial.distance.jensenshannon does, m = (p + q) / 2, sqrt((KL(p||m) + KL(q||m)) / 2),
+// all in fp64 with fixed-order block reductions.
+#include <algorithm>
+
+#include "common.cuh"
+
+using namespace flr;
+
+namespace {
+
+constexpr int GH_THREADS = 256;
+
+__global__ void __launch_bounds__(GH_THREADS) group_item_histogram_kernel(
+    const int32_t *__restrict__ lists, const int32_t *__restrict__ lens, const uint8_t *__restrict__ group,
+    int64_t R, int K, int k_cap, int G, int V, int vocab, unsigned long long *__restrict__ hist) {
+    extern __shared__ unsigned int s_cnt[];                 // [vocab]
+    const int g = blockIdx.y;
+    for (int i = threadIdx.x; i < vocab; i += GH_THREADS) s_cnt[i] = 0u;
+    __syncthreads();
+    // rows of group g: explicit ids (group[r] == g) or, when group == NULL, the rows r % V == g
+    const int64_t stride = static_cast<int64_t>(gridDim.x) * GH_THREADS;
+    const int64_t n_mine = group ? R : (R - g + V - 1) / V;
+    const int64_t n_iter = (n_mine + stride - 1) / stride;
+    for (int64_t it = 0; it < n_iter; ++it) {               // whole warps stay together for the vote
+        const int64_t q = static_cast<int64_t>(blockIdx.x) * GH_THREADS + threadIdx.x + it * stride;
+        int64_t r = -1;
+        if (q < n_mine) {
+            r = group ? q : q * V + g;
+            if (group && group[r] != g) r = -1;
+        }
+        const int len = r >= 0 ? max(0, min(min(lens[r], K), k_cap)) : 0;
+        const int max_len = __reduce_max_sync(0xffffffffu, len);
+        const int32_t *row = lists + (r >= 0 ? r : 0) * K;
+        for (int j = 0; j < max_len; ++j) {
+            int id = -1;
+            if (j < len) {
+                id = row[j];
+                if (static_cast<unsigned>(id) >= static_cast<unsigned>(vocab)) id = -1;
+            }
+            const unsigned peers = __match_any_sync(0xffffffffu, id);
+            if (id >= 0 && (threadIdx.x & 31) == (__ffs(peers) - 1)) atomicAdd(&s_cnt[id], __popc(peers));
+        }
+    }
+    __syncthreads();
+    unsigned long long *h = hist + static_cast<size_t>(g) * vocab;
+    for (int i = threadIdx.x; i < vocab; i += GH_THREADS) {
+        const unsigned int c = s_cnt[i];
+        if (c) atomicAdd(h + i, static_cast<unsigned long long>(c));
+    }
+}
+
+constexpr int JS_THREADS = 256;
+
+// fixed-order block sum of two running values (shared-memory tree); every thread gets the result
+__device__ __forceinline__ void block_sum2(double &a, double &b, double (*s)[2]) {
+    const int t = threadIdx.x;
+    s[t][0] = a; s[t][1] = b;
+    __syncthreads();
+    for (int half = JS_THREADS / 2; half >= 1; half >>= 1) {
+        if (t < half) { s[t][0] += s[t + half][0]; s[t][1] += s[t + half][1]; }
+        __syncthreads();
+    }
+    a = s[0][0]; b = s[0][1];
+    __syncthreads();
+}
+
+__global__ void __launch_bounds__(JS_THREADS) js_distance_kernel(const unsigned long long *__restrict__ hist, int G,
+                                                                 int vocab, double *__restrict__ out,
+                                                                 unsigned char *__restrict__ valid) {
+    __shared__ double s_red[JS_THREADS][2];
+    // pair index -> (i, j), i < j, row-major like the reference's double loop
+    int i = 0, rem = blockIdx.x;
+    while (rem >= G - 1 - i) { rem -= G - 1 - i; ++i; }
+    const int j = i + 1 + rem;
+    const unsigned long long *ci = hist + static_cast<size_t>(i) * vocab, *cj = hist + static_cast<size_t>(j) * vocab;
+    const int t = threadIdx.x;
+
+    double ti = 0.0, tj = 0.0;                                  // group totals (exact integers)
+    for (int x = t; x < vocab; x += JS_THREADS) { ti += static_cast<double>(ci[x]); tj += static_cast<double>(cj[x]); }
+    block_sum2(ti, tj, s_red);
+    if (!(ti > 0.0) || !(tj > 0.0)) {                           // an empty group is skipped (src/utils.py:200)
+        if (t == 0) { out[blockIdx.x] = 0.0; valid[blockIdx.x] = 0; }
+        return;
+    }
+    // p_x = count / total, or 1e-10 for a key only the other group holds (src/utils.py:95-97)
+    auto pq = [&](int x, double &p, double &q) -> bool {
+        const unsigned long long a = ci[x], b = cj[x];
+        if (a == 0ull && b == 0ull) return false;
+        p = a ? static_cast<double>(a) / ti : 1e-10;
+        q = b ? static_cast<double>(b) / tj : 1e-10;
+        return true;
+    };
+    double sp = 0.0, sq = 0.0;                                  // first renormalisation (:99-100)
+    for (int x = t; x < vocab; x += JS_THREADS) { double p, q; if (pq(x, p, q)) { sp += p; sq += q; } }
+    block_sum2(sp, sq, s_red);
+    double sp2 = 0.0, sq2 = 0.0;                                // scipy normalises once more
+    for (int x = t; x < vocab; x += JS_THREADS) { double p, q; if (pq(x, p, q)) { sp2 += p / sp; sq2 += q / sq; } }
+    block_sum2(sp2, sq2, s_red);
+    double left = 0.0, right = 0.0;
+    for (int x = t; x < vocab; x += JS_THREADS) {
+        double p, q;
+        if (pq(x, p, q)) {
+            p = (p / sp) / sp2;
+            q = (q / sq) / sq2;
+            const double m = (p + q) / 2.0;
+            left += p * log(p / m);
+            right += q * log(q / m);
+        }
+    }
+    block_sum2(left, right, s_red);
+    if (t == 0) {
+        out[blockIdx.x] = sqrt((left + right) / 2.0);
+        valid[blockIdx.x] = 1;
+    }
+}
+
+}  // namespace
+
+extern "C" int flr_group_item_histogram(const int32_t *lists, const int32_t *lens, const uint8_t *group, int64_t R,
+                                        int K, int k_cap, int n_groups, int vocab, uint64_t *hist, void *stream_) {
+    FLR_REQUIRE(R >= 0 && K >= 1 && k_cap >= 1 && n_groups >= 1 && n_groups <= 256 && vocab >= 1, FLR_E_INVALID,
+                "group_item_histogram: bad shape");
+    FLR_REQUIRE(static_cast<size_t>(vocab) * 4 <= 200 * 1024, FLR_E_UNSUPPORTED,
+                "group_item_histogram: vocab %d does not fit the shared-memory counters (max 51200)", vocab);
+    if (R == 0) return FLR_OK;
+    FLR_REQUIRE(lists && lens && hist, FLR_E_INVALID, "group_item_histogram: null pointer");
+    const size_t smem = static_cast<size_t>(vocab) * sizeof(unsigned int);
+    if (smem > 48 * 1024)
+        FLR_CUDA(cudaFuncSetAttribute(group_item_histogram_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      static_cast<int>(smem)));
+    const int64_t rows_per_group = group ? R : (R + n_groups - 1) / n_groups;
+    const int sms = device_sm_count();
+    int bx = static_cast<int>(std::min<int64_t>((rows_per_group + GH_THREADS - 1) / GH_THREADS,
+                                                std::max(1, sms * 8 / n_groups)));
+    bx = std::max(bx, 1);
+    dim3 grid(bx, n_groups);
+    group_item_histogram_kernel<<<grid, GH_THREADS, smem, static_cast<cudaStream_t>(stream_)>>>(
+        lists, lens, group, R, K, k_cap, n_groups, n_groups, vocab, reinterpret_cast<unsigned long long *>(hist));
+    FLR_LAUNCH_CHECK("group_item_histogram_kernel");
+    return FLR_OK;
+}
+
+extern "C" int flr_js_distance_matrix(const uint64_t *hist, int n_groups, int vocab, double *out_dist,
+                                      uint8_t *out_valid, void *stream_) {
+    FLR_REQUIRE(n_groups >= 1 && vocab >= 1, FLR_E_INVALID, "js_distance_matrix: bad shape");
+    const int n_pairs = n_groups * (n_groups - 1) / 2;
+    if (n_pairs == 0) return FLR_OK;
+    FLR_REQUIRE(hist && out_dist && out_valid, FLR_E_INVALID, "js_distance_matrix: null pointer");
+    js_distance_kernel<<<n_pairs, JS_THREADS, 0, static_cast<cudaStream_t>(stream_)>>>(
+        reinterpret_cast<const unsigned long long *>(hist), n_groups, vocab, out_dist, out_valid);
+    FLR_LAUNCH_CHECK("js_distance_kernel");
+    return FLR_OK;
+}

@@ -20,7 +20,7 @@ from ._lib import (DTYPE_F32, DTYPE_F64, EMPTY_ANY_IS_ZERO, EMPTY_BOTH_IS_ONE, M
 __all__ = [
     "list_metrics", "ListMetrics", "pair_jaccard", "cosine_nonconformity", "radix_select",
     "threshold_schedule", "violation_detect", "conformal_keep_len", "normalize_rows_bf16",
-    "pair_similarity", "synth_lists", "synth_embeddings", "synth_lists_host",
+    "pair_similarity", "group_item_histogram", "js_distance_matrix", "synth_lists", "synth_embeddings", "synth_lists_host",
     "synth_embeddings_host", "zipf_cdf_host", "device_info",
     "EMPTY_ANY_IS_ZERO", "EMPTY_BOTH_IS_ONE",
 ]
@@ -243,6 +243,43 @@ def conformal_keep_len(lens, thr, groups: Optional[torch.Tensor] = None) -> torc
     out = torch.empty(lens.shape, dtype=torch.int32, device=lens.device)
     _lib.call("flr_conformal_keep_len", _ptr(lens), _ptr(groups), _ptr(thr), lens.numel(), _ptr(out), _stream())
     return out
+
+
+# ------------------------------------------------------------------------------ demographic parity
+def group_item_histogram(lists, lens, *, vocab: int, n_groups: int, groups: Optional[torch.Tensor] = None,
+                         k_cap: Optional[int] = None, hist: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """hist[g, x] += occurrences of item x in the rows of group g (src/utils.py:180-187).
+    lists int32 [..., K] (rows = all leading dims); groups uint8 per row, or None when the rows are laid
+    out [U, V, K] and row r belongs to group r % n_groups.  Returns int64 [n_groups, vocab]."""
+    lists = _dev(lists, torch.int32, "lists")
+    lens = _dev(lens, torch.int32, "lens")
+    K = lists.shape[-1]
+    R = lists.numel() // K
+    if lens.numel() != R:
+        raise ValueError("lens must hold one length per row")
+    if groups is not None:
+        groups = _dev(groups, torch.uint8, "groups")
+        if groups.numel() != R:
+            raise ValueError("groups must hold one id per row")
+    if hist is None:
+        hist = torch.zeros((n_groups, vocab), dtype=torch.int64, device=lists.device)
+    else:
+        _dev(hist, torch.int64, "hist")
+    _lib.call("flr_group_item_histogram", _ptr(lists), _ptr(lens), _ptr(groups), R, K, K if k_cap is None else int(k_cap),
+              int(n_groups), int(vocab), _ptr(hist), _stream())
+    return hist
+
+
+def js_distance_matrix(hist):
+    """Jensen-Shannon distances (src/utils.py:89-102) between every pair of group histograms, i < j in
+    row-major order: (float64 [G(G-1)/2], uint8 validity -- 0 where a group is empty)."""
+    hist = _dev(hist, torch.int64, "hist")
+    G, vocab = hist.shape
+    n_pairs = G * (G - 1) // 2
+    dist = torch.zeros(max(n_pairs, 1), dtype=torch.float64, device=hist.device)
+    valid = torch.zeros(max(n_pairs, 1), dtype=torch.uint8, device=hist.device)
+    _lib.call("flr_js_distance_matrix", _ptr(hist), G, vocab, _ptr(dist), _ptr(valid), _stream())
+    return dist[:n_pairs], valid[:n_pairs]
 
 
 # ------------------------------------------------------------------------------ config 4

@@ -21,3 +21,8 @@ def measure_individual_fairness(profiles: List[Dict], recommendations: Dict[str,
         "mean_similarity": fairness_score,
         "std_similarity": np.std(similarities) if similarities else 0,
     }
+
+
+def measure_demographic_parity(recommendations_by_group) -> Tuple[float, Dict]:
+    """Demographic parity across groups -- reference: src/phase1_bias_detection.py:214-218."""
+    return utils.calculate_demographic_parity(recommendations_by_group)

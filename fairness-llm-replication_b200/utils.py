@@ -102,3 +102,49 @@ def create_profile_pairs(profiles: List[Dict], differing_attribute: Optional[str
         ii, jj = np.nonzero(ok)
         pairs.extend((ids[s + i], ids[j]) for i, j in zip(ii.tolist(), jj.tolist()))
     return pairs
+
+
+def calculate_demographic_parity(recommendations_by_group: Dict[str, List[List[str]]],
+                                 genre_mapping: Optional[Dict[str, List[str]]] = None) -> Tuple[float, Dict]:
+    """Demographic parity -- reference: src/utils.py:172-215 (``genre_mapping`` is accepted and unused
+    there too).
+
+    Per group the distribution of recommended items over all its lists (every occurrence counts), the
+    Jensen-Shannon distance between every two non-empty groups, score = 1 - mean distance.  Counting
+    and the distances run on the GPU (``flr_group_item_histogram``, ``flr_js_distance_matrix``); the
+    probabilities in ``'distributions'`` are count / total in float64, exactly the reference's values.
+    The distances agree with the reference to ~1e-15 relative: the reference itself sums in the
+    arbitrary order of a Python ``set`` of titles.
+    """
+    vocab = encode.Vocabulary()
+    names = list(recommendations_by_group.keys())
+    rows, row_group = [], []
+    for g, name in enumerate(names):
+        for recs in recommendations_by_group[name]:
+            rows.append(vocab.encode(recs))
+            row_group.append(g)
+    G = len(names)
+    items = list(vocab.index.keys())
+    counts = np.zeros((G, max(len(items), 1)), np.int64)
+    divergences: List[float] = []
+    if rows and G <= 256:
+        dev = _device()
+        ids, lens = encode.pack_rows(rows)
+        hist = ops.group_item_histogram(torch.from_numpy(ids).to(dev), torch.from_numpy(lens).to(dev),
+                                        vocab=counts.shape[1], n_groups=G,
+                                        groups=torch.from_numpy(np.asarray(row_group, np.uint8)).to(dev))
+        if G >= 2:
+            dist, valid = ops.js_distance_matrix(hist)
+            divergences = [float(d) for d, ok in zip(dist.cpu().tolist(), valid.cpu().tolist()) if ok]
+        counts = hist.cpu().numpy()
+    elif rows:
+        raise ValueError("calculate_demographic_parity: more than 256 groups are not supported on the GPU path")
+    distributions = {}
+    for g, name in enumerate(names):
+        total = int(counts[g].sum())
+        distributions[name] = ({items[x]: int(c) / total for x, c in enumerate(counts[g].tolist()) if c}
+                               if total > 0 else {})
+    avg_divergence = np.mean(divergences) if divergences else 0
+    parity_score = 1 - avg_divergence
+    return parity_score, {"divergences": divergences, "distributions": distributions,
+                          "avg_divergence": avg_divergence}

@@ -187,6 +187,23 @@ int flr_conformal_keep_len(const int32_t *lens, const uint8_t *group, const doub
                            int64_t U, int32_t *out_keep, void *stream);
 
 /* ---------------------------------------------------------------------------------------
+ * Demographic parity.
+ * flr_group_item_histogram replaces the counting loop of utils.calculate_demographic_parity
+ * (src/utils.py:180-187): hist[g, x] += occurrences of item x in the rows of group g, every
+ * occurrence counted.  lists int32 [R, K], lens int32 [R]; group uint8 [R], or NULL for the dense
+ * [U, V, K] layout where row r belongs to group r % n_groups.  hist uint64 [n_groups, vocab] is
+ * added to (caller zeroes it; multi-GPU callers all-reduce it afterwards).
+ * flr_js_distance_matrix replaces calculate_js_divergence (src/utils.py:89-102) for every group
+ * pair i < j in row-major order: out_dist double [G(G-1)/2], out_valid uint8 (0 where a group is
+ * empty and the reference skips the pair, src/utils.py:200).
+ * ------------------------------------------------------------------------------------- */
+int flr_group_item_histogram(const int32_t *lists, const int32_t *lens, const uint8_t *group,
+                             int64_t R, int K, int k_cap, int n_groups, int vocab,
+                             uint64_t *hist, void *stream);
+int flr_js_distance_matrix(const uint64_t *hist, int n_groups, int vocab, double *out_dist,
+                           uint8_t *out_valid, void *stream);
+
+/* ---------------------------------------------------------------------------------------
  * Dense per-user similarity matrices S[u] = X[u] X[u]^T (config 4; no reference code).
  *   x bf16 [U, M, D] (rows L2-normalised by flr_normalize_rows_bf16), out float [U, M, M].
  *   tcgen05.mma (kind::f16, fp32 accumulate in TMEM), operands staged by TMA.

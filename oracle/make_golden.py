@@ -182,6 +182,27 @@ def main():
                              "columns": {c: [v if isinstance(v, str) else float(v) for v in df[c]]
                                          for c in df.columns}}
 
+    # ---- N1: calculate_demographic_parity / calculate_js_divergence (src/utils.py:172, :89) ----
+    # (appended last so that every seeded case above keeps its values)
+    cases = []
+    inputs = [{"g1": [["x", "y"], ["x", "z"]], "g2": [["x", "y"], ["y", "w"]]}, {}, {"solo": [["a"]]},
+              {"a": [[]], "b": [["m"]]}, {"a": [["m", "m", "n"]], "b": [["m"]], "c": [["q", "q"]]}]
+    for _ in range(8):
+        names = rng.sample(["male", "female", "non-binary", "18-24", "25-34", "35-44", "55+"], rng.randint(2, 6))
+        inputs.append({n: [_rand_list(rng, 12, p_empty=0.15, p_dup=0.3) for _ in range(rng.randint(0, 9))]
+                       for n in names})
+    for d in inputs:
+        score, det = utils.calculate_demographic_parity(d)
+        # group order matters (pairs are enumerated i < j) and json.dump sorts keys: keep it as a list
+        cases.append({"groups": [[k, v] for k, v in d.items()], "score": float(score),
+                      "divergences": [float(x) for x in det["divergences"]],
+                      "avg_divergence": float(det["avg_divergence"]),
+                      "distributions": {k: {i: float(v) for i, v in dist.items()} for k, dist in det["distributions"].items()}})
+    g["demographic_parity"] = cases
+    g["js_divergence"] = [{"p": {"a": 1}, "q": {"b": 1}, "js": float(utils.calculate_js_divergence({"a": 1}, {"b": 1}))},
+                          {"p": {"a": 0.5, "b": 0.3, "c": 0.2}, "q": {"a": 0.4, "b": 0.4, "c": 0.2},
+                           "js": float(utils.calculate_js_divergence({"a": 0.5, "b": 0.3, "c": 0.2}, {"a": 0.4, "b": 0.4, "c": 0.2}))}]
+
     with open(OUT, "w") as f:
         json.dump(g, f, indent=0, sort_keys=True)
     print("wrote", OUT, os.path.getsize(OUT), "bytes")

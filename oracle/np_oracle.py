@@ -430,3 +430,48 @@ def radix_select_sharded(shards, alpha=0.1, all_reduce=lambda h: h):
         less += before
         equal = int(hist[b])
     return radix_unkey_f32(np.uint32(prefix)), n, k, less, equal
+
+
+# --------------------------------------------------------------------------
+# demographic parity
+# --------------------------------------------------------------------------
+def group_item_counts(lists, lens, groups, n_groups, vocab, k_cap=None):
+    """counts[g, x] = occurrences of item x over all rows of group g, WITH multiplicity
+    (src/utils.py:180-187 counts every occurrence; nothing is de-duplicated here)."""
+    lists = np.asarray(lists)
+    R, K = lists.shape
+    lens = np.minimum(np.asarray(lens).reshape(R), K if k_cap is None else k_cap)
+    groups = np.asarray(groups).reshape(R)
+    live = np.arange(K)[None, :] < lens[:, None]
+    live &= (lists >= 0) & (lists < vocab)
+    flat = (groups[:, None].astype(np.int64) * vocab + np.where(live, lists, 0))[live]
+    return np.bincount(flat, minlength=n_groups * vocab).reshape(n_groups, vocab).astype(np.int64)
+
+
+def js_distance_from_counts(ci, cj):
+    """calculate_js_divergence (src/utils.py:89-102) on two count vectors over a shared item
+    vocabulary: keys = items either group holds; p = count/total or 1e-10 when missing; renormalise;
+    scipy's jensenshannon (normalise again, natural log, square root)."""
+    ci = np.asarray(ci, np.float64)
+    cj = np.asarray(cj, np.float64)
+    keys = (ci > 0) | (cj > 0)
+    p = np.where(ci > 0, ci / ci.sum(), 1e-10)[keys]
+    q = np.where(cj > 0, cj / cj.sum(), 1e-10)[keys]
+    p = p / p.sum()
+    q = q / q.sum()
+    p = p / np.sum(p)
+    q = q / np.sum(q)
+    m = (p + q) / 2.0
+    return float(np.sqrt((np.sum(p * np.log(p / m)) + np.sum(q * np.log(q / m))) / 2.0))
+
+
+def demographic_parity_from_counts(counts):
+    """Score and pairwise distances (i < j, both groups non-empty, row-major order) as
+    calculate_demographic_parity (src/utils.py:196-208) produces them."""
+    counts = np.asarray(counts)
+    G = counts.shape[0]
+    nonempty = counts.sum(1) > 0
+    div = [js_distance_from_counts(counts[i], counts[j])
+           for i in range(G) for j in range(i + 1, G) if nonempty[i] and nonempty[j]]
+    avg = float(np.mean(div)) if div else 0.0
+    return 1.0 - avg, div

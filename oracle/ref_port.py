@@ -147,3 +147,46 @@ def nonconformity_records(profiles, recommendations, ground_truth_ratings=None, 
             for k, v in zip(cols, (pid, p["gender"], movie, conf, actual, abs(conf - actual))):
                 cols[k].append(v)
     return cols
+
+
+def calculate_js_divergence(p: Dict[str, float], q: Dict[str, float]) -> float:
+    """src/utils.py:89-102 -- Jensen-Shannon DISTANCE (square root of the divergence, natural log, as
+    scipy.spatial.distance.jensenshannon returns it) over the union of the two key sets, a missing key
+    counting 1e-10, each side renormalised first."""
+    keys = set(list(p.keys()) + list(q.keys()))
+    pa = np.array([p.get(k, 1e-10) for k in keys])
+    qa = np.array([q.get(k, 1e-10) for k in keys])
+    return float(_js_distance(pa / pa.sum(), qa / qa.sum()))
+
+
+def _js_distance(p: np.ndarray, q: np.ndarray) -> float:
+    """scipy.spatial.distance.jensenshannon(p, q) restated (scipy 1.x): normalise, m = (p+q)/2,
+    sqrt((KL(p||m) + KL(q||m)) / 2)."""
+    p = p / np.sum(p)
+    q = q / np.sum(q)
+    m = (p + q) / 2.0
+    left = np.where(p > 0, p * np.log(np.where(p > 0, p, 1.0) / m), 0.0)
+    right = np.where(q > 0, q * np.log(np.where(q > 0, q, 1.0) / m), 0.0)
+    return np.sqrt((np.sum(left) + np.sum(right)) / 2.0)
+
+
+def calculate_demographic_parity(recommendations_by_group, genre_mapping=None):
+    """src/utils.py:172-215 -- per group the item distribution over ALL its lists (with multiplicity),
+    every pair of non-empty groups compared by calculate_js_divergence, score = 1 - mean distance
+    (no pair -> avg 0 -> score 1)."""
+    distributions = {}
+    for group, recs_list in recommendations_by_group.items():
+        counts: Dict[str, int] = {}
+        for recs in recs_list:
+            for item in recs:
+                counts[item] = counts.get(item, 0) + 1
+        total = sum(counts.values())
+        distributions[group] = {k: c / total for k, c in counts.items()} if total > 0 else {}
+    groups = list(distributions.keys())
+    divergences = []
+    for i in range(len(groups)):
+        for j in range(i + 1, len(groups)):
+            if distributions[groups[i]] and distributions[groups[j]]:
+                divergences.append(calculate_js_divergence(distributions[groups[i]], distributions[groups[j]]))
+    avg = np.mean(divergences) if divergences else 0
+    return 1 - avg, {"divergences": divergences, "distributions": distributions, "avg_divergence": avg}

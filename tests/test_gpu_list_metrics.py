@@ -262,3 +262,43 @@ def test_pair_jaccard_bitsets():
         want = O.pair_jaccard(lists, lens)
         assert np.array_equal(inter.cpu().numpy(), want["inter"])
         assert np.array_equal(sizes.cpu().numpy(), want["sizes"])
+
+
+# ---- N1: demographic parity ---------------------------------------------------------------------
+def test_group_item_histogram_and_js_distances():
+    from fairness_llm_replication_b200 import ops
+    rng = np.random.default_rng(31)
+    U, V, K, vocab = 3001, 31, 20, 3706
+    _, _, lists, lens = ops.synth_lists_host(20251203, 0, U, V, K, vocab)
+    lists = lists.copy()
+    lists[5, 3, :4] = 7                                            # multiplicity must be counted
+    t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).cuda()
+    hist = ops.group_item_histogram(t(lists), t(lens), vocab=vocab, n_groups=V)          # implicit groups r % V
+    groups = np.tile(np.arange(V, dtype=np.uint8), U)
+    want = O.group_item_counts(lists.reshape(-1, K), lens.reshape(-1), groups, V, vocab)
+    assert np.array_equal(hist.cpu().numpy(), want)
+    perm = rng.permutation(U * V)                                   # explicit group ids, shuffled rows
+    hist2 = ops.group_item_histogram(t(lists.reshape(-1, K)[perm]), t(lens.reshape(-1)[perm]), vocab=vocab,
+                                     n_groups=V, groups=t(groups[perm]))
+    assert torch.equal(hist, hist2)
+    hist3 = ops.group_item_histogram(t(lists), t(lens), vocab=vocab, n_groups=V, k_cap=10)
+    assert np.array_equal(hist3.cpu().numpy(),
+                          O.group_item_counts(lists.reshape(-1, K), lens.reshape(-1), groups, V, vocab, k_cap=10))
+    hist[4] = 0                                                     # an empty group: its pairs are skipped
+    dist, valid = ops.js_distance_matrix(hist)
+    score, div = O.demographic_parity_from_counts(hist.cpu().numpy())
+    got = [d for d, ok in zip(dist.cpu().tolist(), valid.cpu().tolist()) if ok]
+    assert len(got) == len(div) == 30 * 29 // 2
+    np.testing.assert_allclose(got, div, rtol=1e-12)
+
+
+def test_dropin_demographic_parity(golden):
+    from fairness_llm_replication_b200 import utils, phase1_bias_detection as p1
+    for c in golden["demographic_parity"]:
+        score, det = utils.calculate_demographic_parity(dict(c["groups"]))
+        assert det["distributions"] == c["distributions"]              # count / total: exact
+        assert det["divergences"] == pytest.approx(c["divergences"], rel=1e-12, abs=1e-15)
+        assert float(score) == pytest.approx(c["score"], rel=1e-12)
+        assert float(det["avg_divergence"]) == pytest.approx(c["avg_divergence"], rel=1e-12, abs=1e-15)
+        s2, _ = p1.measure_demographic_parity(dict(c["groups"]))
+        assert float(s2) == float(score)

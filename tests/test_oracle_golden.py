@@ -215,3 +215,29 @@ def test_bf16_round_and_pair_similarity():
     S = O.pair_similarity(xh)
     assert np.allclose(np.diagonal(S, axis1=1, axis2=2), 1.0, atol=1e-2)
     assert np.allclose(S, np.swapaxes(S, 1, 2))
+
+
+def test_demographic_parity_port_and_counts_oracle(golden):
+    for c in golden["js_divergence"]:
+        assert R.calculate_js_divergence(c["p"], c["q"]) == pytest.approx(c["js"], rel=1e-13)
+    for c in golden["demographic_parity"]:
+        score, det = R.calculate_demographic_parity(dict(c["groups"]))
+        assert det["distributions"] == c["distributions"]
+        assert det["divergences"] == pytest.approx(c["divergences"], rel=1e-12, abs=1e-15)
+        assert float(score) == pytest.approx(c["score"], rel=1e-12)
+        # numpy restatement on id-encoded rows
+        vocab, rows, grp = {}, [], []
+        for g, (name, lists) in enumerate(c["groups"]):
+            for l in lists:
+                rows.append([vocab.setdefault(x, len(vocab)) for x in l]); grp.append(g)
+        G = len(c["groups"])
+        if not rows:
+            continue
+        K = max([len(r) for r in rows] + [1])
+        arr = np.full((len(rows), K), -1, np.int32)
+        for i, r in enumerate(rows):
+            arr[i, :len(r)] = r
+        counts = O.group_item_counts(arr, [len(r) for r in rows], grp, G, max(len(vocab), 1))
+        s2, div = O.demographic_parity_from_counts(counts)
+        assert div == pytest.approx(c["divergences"], rel=1e-12, abs=1e-15)
+        assert s2 == pytest.approx(c["score"], rel=1e-12)
