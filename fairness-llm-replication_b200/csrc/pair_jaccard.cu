@@ -1,11 +1,11 @@
 // All-pairs list intersections between the M lists of each user (config 4, "pairwise
 // list-similarity"; no reference code -- definition: oracle/np_oracle.py:pair_jaccard).
 //
-// One CTA per user: the M ranked lists become M `vocab`-bit item sets in shared memory
-// (row stride padded to an odd word count so a warp's 32 rows hit 32 banks), every pair's
-// intersection is a __popc sum over AND-ed words, and the M x M matrix is assembled in
-// shared memory so the global store is one coalesced sweep.  Each thread owns a 2 x 2 block
-// of pairs so every word loaded from shared memory feeds two ANDs.
+// One CTA per user: the M ranked lists become M item bit sets in shared memory (row stride padded to
+// an odd word count so a warp's 32 rows hit 32 banks), every pair's intersection is a __popc sum over
+// AND-ed words, and the M x M matrix is assembled in shared memory so the global store is one
+// coalesced sweep.  Each thread owns a 2 x 2 block of pairs so every word loaded from shared memory
+// feeds two ANDs.
 #include <algorithm>
 
 #include "common.cuh"
@@ -16,26 +16,55 @@ namespace {
 
 constexpr int PJ_THREADS = 256;
 
+// Per user the lists only touch a few hundred distinct items out of `vocab`, so the items are first
+// renumbered into a dense per-user universe (claim a slot in a vocab-sized table with one CAS per
+// element, number the winners with a shared counter); the bit sets are then n_local bits wide
+// instead of vocab bits, which divides the popcount work by 116 / ceil(n_local / 32).
 __global__ void __launch_bounds__(PJ_THREADS) pair_jaccard_kernel(const int32_t *__restrict__ lists,
                                                                   const int32_t *__restrict__ lens, int64_t U, int M,
-                                                                  int K, int vocab, int W, int Wp,
+                                                                  int K, int vocab, int Wmax,
                                                                   int32_t *__restrict__ out_inter,
                                                                   int32_t *__restrict__ out_sizes) {
     extern __shared__ __align__(16) unsigned int s_mem[];
-    unsigned int *s_bits = s_mem;                               // [M][Wp]
-    int *s_inter = reinterpret_cast<int *>(s_mem + ((M * Wp + 3) & ~3));   // [M][M]
+    constexpr unsigned EMPTY = 0xFFFFFFFFu, PENDING = 0xFFFFFFFEu;
+    unsigned int *s_tab = s_mem;                                           // [vocab] item -> local index
+    unsigned int *s_bits = s_tab + ((vocab + 3) & ~3);                      // [M][Wp], Wp odd
+    const int Wp_max = Wmax | 1;
+    int *s_inter = reinterpret_cast<int *>(s_bits + ((M * Wp_max + 3) & ~3));   // [M][M]
+    __shared__ unsigned int s_count;
     const int t = threadIdx.x;
     const int Mh = (M + 1) >> 1;                                // 2x2 blocks per side
 
+    for (int i = t; i < vocab; i += PJ_THREADS) s_tab[i] = EMPTY;
+    for (int i = t; i < M * Wp_max; i += PJ_THREADS) s_bits[i] = 0u;
+    if (t == 0) s_count = 0u;
+    __syncthreads();
+
     for (int64_t u = blockIdx.x; u < U; u += gridDim.x) {
-        for (int i = t; i < M * Wp; i += PJ_THREADS) s_bits[i] = 0u;
-        __syncthreads();
         const int32_t *L = lists + u * M * K;
+        const int32_t *ln = lens + u * M;
+        // pass 1: the first thread to touch an item claims it and takes the next local index
         for (int i = t; i < M * K; i += PJ_THREADS) {
             const int m = i / K, j = i - m * K;
-            if (j < min(max(lens[u * M + m], 0), K)) {
+            if (j < min(max(ln[m], 0), K)) {
                 const unsigned id = static_cast<unsigned>(L[i]);
-                if (id < static_cast<unsigned>(vocab)) atomicOr(&s_bits[m * Wp + (id >> 5)], 1u << (id & 31u));
+                if (id < static_cast<unsigned>(vocab) && s_tab[id] == EMPTY &&
+                    atomicCAS(&s_tab[id], EMPTY, PENDING) == EMPTY)
+                    s_tab[id] = atomicAdd(&s_count, 1u);
+            }
+        }
+        __syncthreads();
+        const int W = static_cast<int>((s_count + 31u) >> 5);             // words actually used (<= Wmax)
+        const int Wp = W | 1;                                              // odd stride: a warp's rows hit 32 banks
+        // pass 2: set bits in the dense universe
+        for (int i = t; i < M * K; i += PJ_THREADS) {
+            const int m = i / K, j = i - m * K;
+            if (j < min(max(ln[m], 0), K)) {
+                const unsigned id = static_cast<unsigned>(L[i]);
+                if (id < static_cast<unsigned>(vocab)) {
+                    const unsigned l = s_tab[id];
+                    atomicOr(&s_bits[m * Wp + (l >> 5)], 1u << (l & 31u));
+                }
             }
         }
         __syncthreads();
@@ -63,6 +92,14 @@ __global__ void __launch_bounds__(PJ_THREADS) pair_jaccard_kernel(const int32_t 
         for (int i = t; i < M * M; i += PJ_THREADS) dst[i] = s_inter[i];
         if (out_sizes)
             for (int m = t; m < M; m += PJ_THREADS) out_sizes[u * M + m] = s_inter[m * M + m];
+        // restore: forget this user's items, wipe the words that were used
+        for (int i = t; i < M * K; i += PJ_THREADS) {
+            const unsigned id = static_cast<unsigned>(L[i]);
+            const int m = i / K, j = i - m * K;
+            if (j < min(max(ln[m], 0), K) && id < static_cast<unsigned>(vocab)) s_tab[id] = EMPTY;
+        }
+        for (int i = t; i < M * Wp; i += PJ_THREADS) s_bits[i] = 0u;
+        if (t == 0) s_count = 0u;
         __syncthreads();
     }
 }
@@ -74,16 +111,19 @@ extern "C" int flr_pair_jaccard(const int32_t *lists, const int32_t *lens, int64
     FLR_REQUIRE(U >= 0 && M >= 1 && K >= 1 && vocab >= 1, FLR_E_INVALID, "pair_jaccard: bad shape");
     if (U == 0) return FLR_OK;
     FLR_REQUIRE(lists && lens && out_inter, FLR_E_INVALID, "pair_jaccard: null pointer");
-    const int W = (vocab + 31) / 32, Wp = W | 1;
-    const size_t smem = (static_cast<size_t>((M * Wp + 3) & ~3) + static_cast<size_t>(M) * M) * 4;
-    FLR_REQUIRE(smem <= 227 * 1024, FLR_E_UNSUPPORTED,
-                "pair_jaccard: M=%d lists of %d-bit sets need %zu B of shared memory (max 232448)", M, vocab, smem);
+    // a user's M lists hold at most M*K distinct items: that bounds the dense universe
+    const int Wmax = static_cast<int>((std::min<int64_t>(static_cast<int64_t>(M) * K, vocab) + 31) / 32);
+    const size_t smem = (static_cast<size_t>((vocab + 3) & ~3) + static_cast<size_t>((M * (Wmax | 1) + 3) & ~3) +
+                         static_cast<size_t>(M) * M) * 4;
+    FLR_REQUIRE(smem <= 226 * 1024, FLR_E_UNSUPPORTED,
+                "pair_jaccard: M=%d lists of up to %d items over %d ids need %zu B of shared memory (max 231424)", M, K,
+                vocab, smem);
     FLR_CUDA(cudaFuncSetAttribute(pair_jaccard_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                   static_cast<int>(smem)));
-    const int per_sm = std::max<int>(1, static_cast<int>((227 * 1024) / (smem + 1024)));
+    const int per_sm = std::max<int>(1, static_cast<int>((226 * 1024) / (smem + 1024)));
     const int grid = static_cast<int>(std::min<int64_t>(U, static_cast<int64_t>(device_sm_count()) * per_sm));
-    pair_jaccard_kernel<<<grid, PJ_THREADS, smem, static_cast<cudaStream_t>(stream_)>>>(lists, lens, U, M, K, vocab, W,
-                                                                                        Wp, out_inter, out_sizes);
+    pair_jaccard_kernel<<<grid, PJ_THREADS, smem, static_cast<cudaStream_t>(stream_)>>>(lists, lens, U, M, K, vocab,
+                                                                                        Wmax, out_inter, out_sizes);
     FLR_LAUNCH_CHECK("pair_jaccard_kernel");
     return FLR_OK;
 }
