@@ -138,6 +138,31 @@ __global__ void __launch_bounds__(JS_THREADS) js_distance_kernel(const unsigned 
     }
 }
 
+// Equal opportunity (src/utils.py:254-266) from the same histogram: per group the number of DISTINCT
+// relevant items that were recommended (counter > 0 on a relevant id) and the number of
+// recommendations made (sum of the counters).  One CTA per group, fixed-order reduction.
+__global__ void __launch_bounds__(JS_THREADS) equal_opportunity_kernel(const unsigned long long *__restrict__ hist,
+                                                                       const uint8_t *__restrict__ relevant, int vocab,
+                                                                       unsigned long long *__restrict__ out_relevant,
+                                                                       unsigned long long *__restrict__ out_total) {
+    __shared__ unsigned long long s_r[JS_THREADS], s_t[JS_THREADS];
+    const int g = blockIdx.x, t = threadIdx.x;
+    const unsigned long long *h = hist + static_cast<size_t>(g) * vocab;
+    unsigned long long rel = 0, tot = 0;
+    for (int x = t; x < vocab; x += JS_THREADS) {
+        const unsigned long long c = h[x];
+        tot += c;
+        rel += (c != 0ull && relevant[x] != 0) ? 1ull : 0ull;
+    }
+    s_r[t] = rel; s_t[t] = tot;
+    __syncthreads();
+    for (int half = JS_THREADS / 2; half >= 1; half >>= 1) {
+        if (t < half) { s_r[t] += s_r[t + half]; s_t[t] += s_t[t + half]; }
+        __syncthreads();
+    }
+    if (t == 0) { out_relevant[g] = s_r[0]; out_total[g] = s_t[0]; }
+}
+
 }  // namespace
 
 extern "C" int flr_group_item_histogram(const int32_t *lists, const int32_t *lens, const uint8_t *group, int64_t R,
@@ -173,5 +198,17 @@ extern "C" int flr_js_distance_matrix(const uint64_t *hist, int n_groups, int vo
     js_distance_kernel<<<n_pairs, JS_THREADS, 0, static_cast<cudaStream_t>(stream_)>>>(
         reinterpret_cast<const unsigned long long *>(hist), n_groups, vocab, out_dist, out_valid);
     FLR_LAUNCH_CHECK("js_distance_kernel");
+    return FLR_OK;
+}
+
+extern "C" int flr_equal_opportunity_counts(const uint64_t *hist, const uint8_t *relevant, int n_groups, int vocab,
+                                            uint64_t *out_relevant, uint64_t *out_total, void *stream_) {
+    FLR_REQUIRE(n_groups >= 0 && vocab >= 1, FLR_E_INVALID, "equal_opportunity_counts: bad shape");
+    if (n_groups == 0) return FLR_OK;
+    FLR_REQUIRE(hist && relevant && out_relevant && out_total, FLR_E_INVALID, "equal_opportunity_counts: null pointer");
+    equal_opportunity_kernel<<<n_groups, JS_THREADS, 0, static_cast<cudaStream_t>(stream_)>>>(
+        reinterpret_cast<const unsigned long long *>(hist), relevant, vocab,
+        reinterpret_cast<unsigned long long *>(out_relevant), reinterpret_cast<unsigned long long *>(out_total));
+    FLR_LAUNCH_CHECK("equal_opportunity_kernel");
     return FLR_OK;
 }

@@ -20,7 +20,7 @@ from ._lib import (DTYPE_F32, DTYPE_F64, EMPTY_ANY_IS_ZERO, EMPTY_BOTH_IS_ONE, M
 __all__ = [
     "list_metrics", "ListMetrics", "pair_jaccard", "cosine_nonconformity", "radix_select",
     "threshold_schedule", "violation_detect", "conformal_keep_len", "normalize_rows_bf16",
-    "pair_similarity", "group_item_histogram", "js_distance_matrix", "synth_lists", "synth_embeddings", "synth_lists_host",
+    "pair_similarity", "group_item_histogram", "js_distance_matrix", "equal_opportunity_counts", "synth_lists", "synth_embeddings", "synth_lists_host",
     "synth_embeddings_host", "zipf_cdf_host", "device_info",
     "EMPTY_ANY_IS_ZERO", "EMPTY_BOTH_IS_ONE",
 ]
@@ -280,6 +280,20 @@ def js_distance_matrix(hist):
     valid = torch.zeros(max(n_pairs, 1), dtype=torch.uint8, device=hist.device)
     _lib.call("flr_js_distance_matrix", _ptr(hist), G, vocab, _ptr(dist), _ptr(valid), _stream())
     return dist[:n_pairs], valid[:n_pairs]
+
+
+def equal_opportunity_counts(hist, relevant):
+    """Per group: (distinct relevant items recommended, recommendations made) -- src/utils.py:254-266.
+    hist int64 [G, vocab] from ``group_item_histogram``; relevant uint8 [vocab] (non-zero = relevant)."""
+    hist = _dev(hist, torch.int64, "hist")
+    relevant = _dev(relevant, torch.uint8, "relevant")
+    G, vocab = hist.shape
+    if relevant.numel() != vocab:
+        raise ValueError("relevant must hold one flag per vocabulary id")
+    rel = torch.zeros(G, dtype=torch.int64, device=hist.device)
+    tot = torch.zeros(G, dtype=torch.int64, device=hist.device)
+    _lib.call("flr_equal_opportunity_counts", _ptr(hist), _ptr(relevant), G, vocab, _ptr(rel), _ptr(tot), _stream())
+    return rel, tot
 
 
 # ------------------------------------------------------------------------------ config 4

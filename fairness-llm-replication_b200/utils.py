@@ -148,3 +148,52 @@ def calculate_demographic_parity(recommendations_by_group: Dict[str, List[List[s
     parity_score = 1 - avg_divergence
     return parity_score, {"divergences": divergences, "distributions": distributions,
                           "avg_divergence": avg_divergence}
+
+
+def _group_histogram(recommendations_by_group):
+    """(group names, item vocabulary, int64 [G, vocab] occurrence counts on the GPU or None if no rows)."""
+    vocab = encode.Vocabulary()
+    names = list(recommendations_by_group.keys())
+    rows, row_group = [], []
+    for g, name in enumerate(names):
+        for recs in recommendations_by_group[name]:
+            rows.append(vocab.encode(recs))
+            row_group.append(g)
+    if len(names) > 256:
+        raise ValueError("more than 256 groups are not supported on the GPU path")
+    if not rows:
+        return names, vocab, None
+    dev = _device()
+    ids, lens = encode.pack_rows(rows)
+    hist = ops.group_item_histogram(torch.from_numpy(ids).to(dev), torch.from_numpy(lens).to(dev),
+                                    vocab=max(len(vocab), 1), n_groups=len(names),
+                                    groups=torch.from_numpy(np.asarray(row_group, np.uint8)).to(dev))
+    return names, vocab, hist
+
+
+def calculate_equal_opportunity(recommendations_by_group: Dict[str, List[List[str]]],
+                                relevant_items: set) -> Tuple[float, Dict[str, float]]:
+    """Equal opportunity -- reference: src/utils.py:246-275.
+
+    Per group: distinct relevant items recommended / recommendations made (0.0 for a group without
+    recommendations); fairness = 1 / (1 + population variance of the group scores).  The two integer
+    counts per group come from the GPU; the ratios, ``np.var`` and the final expression are the
+    reference's own, so the result is bit-identical.
+    """
+    names, vocab, hist = _group_histogram(recommendations_by_group)
+    opportunity_scores: Dict[str, float] = {}
+    if hist is None:
+        opportunity_scores = {name: 0.0 for name in names}
+    else:
+        flags = np.zeros(hist.shape[1], np.uint8)
+        for item in relevant_items:
+            i = vocab.index.get(item)
+            if i is not None:
+                flags[i] = 1
+        rel, tot = ops.equal_opportunity_counts(hist, torch.from_numpy(flags).to(hist.device))
+        for name, r, n in zip(names, rel.cpu().tolist(), tot.cpu().tolist()):
+            opportunity_scores[name] = r / n if n > 0 else 0.0
+    scores = list(opportunity_scores.values())
+    variance = np.var(scores) if scores else 0
+    fairness_score = 1 / (1 + variance)
+    return fairness_score, opportunity_scores

@@ -202,6 +202,12 @@ int flr_group_item_histogram(const int32_t *lists, const int32_t *lens, const ui
                              uint64_t *hist, void *stream);
 int flr_js_distance_matrix(const uint64_t *hist, int n_groups, int vocab, double *out_dist,
                            uint8_t *out_valid, void *stream);
+/* Equal opportunity from the same histogram -- replaces the set
+ * intersection and the length count of utils.calculate_equal_opportunity (src/utils.py:254-266):
+ * out_relevant[g] = number of distinct items x with relevant[x] != 0 that group g was recommended,
+ * out_total[g] = number of recommendations made to group g.  relevant uint8 [vocab]. */
+int flr_equal_opportunity_counts(const uint64_t *hist, const uint8_t *relevant, int n_groups, int vocab,
+                                 uint64_t *out_relevant, uint64_t *out_total, void *stream);
 
 /* ---------------------------------------------------------------------------------------
  * Dense per-user similarity matrices S[u] = X[u] X[u]^T (config 4; no reference code).

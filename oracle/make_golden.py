@@ -4,7 +4,9 @@ functions from /root/reference/src on seeded inputs.  Run in the build container
     python -m oracle.make_golden
 
 TEST INFRASTRUCTURE ONLY.  The JSON holds inputs and the reference's outputs; floats
-round-trip exactly through ``repr``.  The reference has no tests of its own
+round-trip exactly through ``repr``.  (The reference's demographic-parity distances are summed in the
+iteration order of a Python ``set`` of titles, so their last digit can change from run to run; the tests
+compare them at 1e-12.)  The reference has no tests of its own
 (SURVEY.md section 4), so these vectors are what pins the oracle and the CUDA path.
 """
 from __future__ import annotations
@@ -202,6 +204,28 @@ def main():
     g["js_divergence"] = [{"p": {"a": 1}, "q": {"b": 1}, "js": float(utils.calculate_js_divergence({"a": 1}, {"b": 1}))},
                           {"p": {"a": 0.5, "b": 0.3, "c": 0.2}, "q": {"a": 0.4, "b": 0.4, "c": 0.2},
                            "js": float(utils.calculate_js_divergence({"a": 0.5, "b": 0.3, "c": 0.2}, {"a": 0.4, "b": 0.4, "c": 0.2}))}]
+
+    # ---- N4: calculate_equal_opportunity / measure_equal_opportunity (src/utils.py:246, phase1:241) ----
+    cases = []
+    qualified = ["Heat", "Fargo", "Alien", "Jaws", "The Matrix"]
+    for c in g["demographic_parity"]:
+        d = {k: v for k, v in c["groups"]}
+        score, by_group = utils.calculate_equal_opportunity(d, set(qualified))
+        entry = {"groups": c["groups"], "relevant": qualified, "score": float(score),
+                 "by_group": [[k, float(v)] for k, v in by_group.items()]}
+        if d:
+            s2, det = p1.measure_equal_opportunity(d, None)
+            entry["measure"] = {"score": float(s2), "variance": float(det["variance"]),
+                                "min_max_ratio": float(det["min_max_ratio"])}
+        cases.append(entry)
+    d = {"a": [["The Matrix", "Heat", "The Matrix"], ["Inception"]], "b": [["Heat"]], "c": [[]]}
+    score, by_group = utils.calculate_equal_opportunity(d, {"The Matrix", "Inception", "Unseen"})
+    s2, det = p1.measure_equal_opportunity(d, None)
+    cases.append({"groups": [[k, v] for k, v in d.items()], "relevant": ["The Matrix", "Inception", "Unseen"],
+                  "score": float(score), "by_group": [[k, float(v)] for k, v in by_group.items()],
+                  "measure": {"score": float(s2), "variance": float(det["variance"]),
+                              "min_max_ratio": float(det["min_max_ratio"])}})
+    g["equal_opportunity"] = cases
 
     with open(OUT, "w") as f:
         json.dump(g, f, indent=0, sort_keys=True)

@@ -190,3 +190,14 @@ def calculate_demographic_parity(recommendations_by_group, genre_mapping=None):
                 divergences.append(calculate_js_divergence(distributions[groups[i]], distributions[groups[j]]))
     avg = np.mean(divergences) if divergences else 0
     return 1 - avg, {"divergences": divergences, "distributions": distributions, "avg_divergence": avg}
+
+
+def calculate_equal_opportunity(recommendations_by_group, relevant_items):
+    """src/utils.py:246-275 -- per group |set(all recs) & relevant| / len(all recs) (0.0 when the group
+    has no recommendation); fairness = 1 / (1 + np.var(scores))."""
+    scores = {}
+    for group, recs_list in recommendations_by_group.items():
+        flat = [x for recs in recs_list for x in recs]
+        scores[group] = len(set(flat) & set(relevant_items)) / len(flat) if flat else 0.0
+    vals = list(scores.values())
+    return 1 / (1 + (np.var(vals) if vals else 0)), scores

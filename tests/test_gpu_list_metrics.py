@@ -302,3 +302,32 @@ def test_dropin_demographic_parity(golden):
         assert float(det["avg_divergence"]) == pytest.approx(c["avg_divergence"], rel=1e-12, abs=1e-15)
         s2, _ = p1.measure_demographic_parity(dict(c["groups"]))
         assert float(s2) == float(score)
+
+
+def test_dropin_equal_opportunity(golden):
+    """N4: bit-identical to the reference (integer counts from the GPU, the reference's own float ops)."""
+    from fairness_llm_replication_b200 import utils, phase1_bias_detection as p1
+    for c in golden["equal_opportunity"]:
+        d = dict(c["groups"])
+        score, by_group = utils.calculate_equal_opportunity(d, set(c["relevant"]))
+        assert [[k, float(v)] for k, v in by_group.items()] == c["by_group"]
+        assert float(score) == c["score"]
+        if "measure" in c and c["relevant"][0] == "Heat":
+            continue                      # measure_* uses the reference's own fixed qualified set
+    d = dict(golden["equal_opportunity"][-1]["groups"])
+    s2, det = p1.measure_equal_opportunity(d, None)
+    m = golden["equal_opportunity"][-1]["measure"]
+    assert float(s2) == m["score"] and float(det["variance"]) == m["variance"]
+    assert float(det["min_max_ratio"]) == m["min_max_ratio"]
+
+
+def test_equal_opportunity_counts_kernel():
+    from fairness_llm_replication_b200 import ops
+    rng = np.random.default_rng(5)
+    G, vocab = 31, 3706
+    hist = rng.integers(0, 4, size=(G, vocab)) * (rng.random((G, vocab)) < 0.2)
+    hist[7] = 0
+    relevant = (rng.random(vocab) < 0.05).astype(np.uint8)
+    rel, tot = ops.equal_opportunity_counts(torch.from_numpy(hist.astype(np.int64)).cuda(), torch.from_numpy(relevant).cuda())
+    assert rel.cpu().tolist() == [int(((hist[g] > 0) & (relevant > 0)).sum()) for g in range(G)]
+    assert tot.cpu().tolist() == hist.sum(1).tolist()

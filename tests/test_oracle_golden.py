@@ -241,3 +241,10 @@ def test_demographic_parity_port_and_counts_oracle(golden):
         s2, div = O.demographic_parity_from_counts(counts)
         assert div == pytest.approx(c["divergences"], rel=1e-12, abs=1e-15)
         assert s2 == pytest.approx(c["score"], rel=1e-12)
+
+
+def test_equal_opportunity_port(golden):
+    for c in golden["equal_opportunity"]:
+        score, by_group = R.calculate_equal_opportunity(dict(c["groups"]), set(c["relevant"]))
+        assert [[k, float(v)] for k, v in by_group.items()] == c["by_group"]
+        assert float(score) == c["score"]
