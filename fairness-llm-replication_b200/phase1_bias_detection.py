@@ -1,7 +1,9 @@
 """Drop-in for the hot-path function of the reference's ``src/phase1_bias_detection.py``."""
 from __future__ import annotations
 
-from typing import Dict, List, Tuple
+import json
+from collections import defaultdict
+from typing import Dict, List, Optional, Tuple
 
 import numpy as np
 
@@ -46,3 +48,38 @@ def measure_equal_opportunity(recommendations_by_group, movies=None) -> Tuple[fl
         'min_max_ratio': min(scores_by_group.values()) / max(scores_by_group.values())
         if scores_by_group and max(scores_by_group.values()) != 0 else 0
     }
+
+
+def calculate_phase1_metrics(profiles: List[Dict], all_recommendations: Dict[str, Dict], movies=None) -> Dict:
+    """Step "[6/6] Calculating fairness metrics" of run_phase1 -- reference:
+    src/phase1_bias_detection.py:343-405: group the lists by gender and by age, then demographic
+    parity (both groupings), individual fairness and equal opportunity (gender grouping).  Returns the
+    ``'metrics'`` block of phase1_results.json.  Every number comes from the GPU path."""
+    recs_by_gender, recs_by_age = defaultdict(list), defaultdict(list)
+    for profile in profiles:
+        pid = profile['id']
+        if pid in all_recommendations and 'recommendations' in all_recommendations[pid]:
+            recs_by_gender[profile['gender']].append(all_recommendations[pid]['recommendations'])
+            recs_by_age[profile['age']].append(all_recommendations[pid]['recommendations'])
+    dp_gender_score, dp_gender_details = measure_demographic_parity(dict(recs_by_gender))
+    dp_age_score, dp_age_details = measure_demographic_parity(dict(recs_by_age))
+    if_score, if_details = measure_individual_fairness(profiles, all_recommendations)
+    eo_score, eo_details = measure_equal_opportunity(dict(recs_by_gender), movies)
+    return {
+        'demographic_parity': {'gender': {'score': dp_gender_score, 'details': dp_gender_details},
+                               'age': {'score': dp_age_score, 'details': dp_age_details}},
+        'individual_fairness': {'score': if_score, 'details': if_details},
+        'equal_opportunity': {'score': eo_score, 'details': eo_details},
+    }
+
+
+def rescore_phase1_results(path_or_results) -> Dict:
+    """Recompute the metrics of a ``phase1_results.json`` written by the reference
+    (schema: src/phase1_bias_detection.py:376-405; loader: src/utils.py:33-49) from its stored
+    profiles and recommendations -- SURVEY.md section 8(f), N2: the on-disk format either side of the
+    hot path.  Accepts a path or an already loaded dict; returns the new ``'metrics'`` block."""
+    results = path_or_results
+    if not isinstance(results, dict):
+        with open(path_or_results, 'r') as f:
+            results = json.load(f)
+    return calculate_phase1_metrics(results['profiles'], results['recommendations'])

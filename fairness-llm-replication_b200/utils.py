@@ -116,29 +116,16 @@ def calculate_demographic_parity(recommendations_by_group: Dict[str, List[List[s
     The distances agree with the reference to ~1e-15 relative: the reference itself sums in the
     arbitrary order of a Python ``set`` of titles.
     """
-    vocab = encode.Vocabulary()
-    names = list(recommendations_by_group.keys())
-    rows, row_group = [], []
-    for g, name in enumerate(names):
-        for recs in recommendations_by_group[name]:
-            rows.append(vocab.encode(recs))
-            row_group.append(g)
+    names, vocab, hist = _group_histogram(recommendations_by_group)
     G = len(names)
     items = list(vocab.index.keys())
     counts = np.zeros((G, max(len(items), 1)), np.int64)
     divergences: List[float] = []
-    if rows and G <= 256:
-        dev = _device()
-        ids, lens = encode.pack_rows(rows)
-        hist = ops.group_item_histogram(torch.from_numpy(ids).to(dev), torch.from_numpy(lens).to(dev),
-                                        vocab=counts.shape[1], n_groups=G,
-                                        groups=torch.from_numpy(np.asarray(row_group, np.uint8)).to(dev))
+    if hist is not None:
         if G >= 2:
             dist, valid = ops.js_distance_matrix(hist)
             divergences = [float(d) for d, ok in zip(dist.cpu().tolist(), valid.cpu().tolist()) if ok]
         counts = hist.cpu().numpy()
-    elif rows:
-        raise ValueError("calculate_demographic_parity: more than 256 groups are not supported on the GPU path")
     distributions = {}
     for g, name in enumerate(names):
         total = int(counts[g].sum())

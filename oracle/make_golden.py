@@ -227,6 +227,24 @@ def main():
                               "min_max_ratio": float(det["min_max_ratio"])}})
     g["equal_opportunity"] = cases
 
+    # ---- N2: the metric step of run_phase1 on a results dict (src/phase1_bias_detection.py:343-374) ----
+    from collections import defaultdict
+    titles = TITLES + ["The Matrix", "Inception", "Goodfellas", "Pulp Fiction"]
+    recs = {p["id"]: {"profile_id": p["id"], "recommendations": rng.sample(titles, rng.randint(0, 10))}
+            for p in prof45 if rng.random() > 0.1}
+    by_gender, by_age = defaultdict(list), defaultdict(list)
+    for p in prof45:
+        if p["id"] in recs:
+            by_gender[p["gender"]].append(recs[p["id"]]["recommendations"])
+            by_age[p["age"]].append(recs[p["id"]]["recommendations"])
+    dpg, _ = p1.measure_demographic_parity(dict(by_gender))
+    dpa, _ = p1.measure_demographic_parity(dict(by_age))
+    ifs, ifd = p1.measure_individual_fairness(prof45, recs)
+    eos, eod = p1.measure_equal_opportunity(dict(by_gender), None)
+    g["phase1_metric_step"] = {"profiles": prof45, "recommendations": recs, "dp_gender": float(dpg), "dp_age": float(dpa),
+                               "if_score": float(ifs), "if_std": float(ifd["std_similarity"]), "eo_score": float(eos),
+                               "eo_by_group": [[k, float(v)] for k, v in eod["opportunity_by_group"].items()]}
+
     with open(OUT, "w") as f:
         json.dump(g, f, indent=0, sort_keys=True)
     print("wrote", OUT, os.path.getsize(OUT), "bytes")

@@ -331,3 +331,20 @@ def test_equal_opportunity_counts_kernel():
     rel, tot = ops.equal_opportunity_counts(torch.from_numpy(hist.astype(np.int64)).cuda(), torch.from_numpy(relevant).cuda())
     assert rel.cpu().tolist() == [int(((hist[g] > 0) & (relevant > 0)).sum()) for g in range(G)]
     assert tot.cpu().tolist() == hist.sum(1).tolist()
+
+
+def test_phase1_metric_step_on_a_results_file(golden, tmp_path):
+    """N2: a phase1_results.json in the reference's schema, re-scored end to end on the GPU path."""
+    import json
+    from fairness_llm_replication_b200 import phase1_bias_detection as p1
+    c = golden["phase1_metric_step"]
+    path = tmp_path / "phase1_results.json"
+    path.write_text(json.dumps({"metadata": {"model": "x"}, "profiles": c["profiles"],
+                                "recommendations": c["recommendations"], "metrics": {}}))
+    m = p1.rescore_phase1_results(str(path))
+    assert float(m["demographic_parity"]["gender"]["score"]) == pytest.approx(c["dp_gender"], rel=1e-12)
+    assert float(m["demographic_parity"]["age"]["score"]) == pytest.approx(c["dp_age"], rel=1e-12)
+    assert float(m["individual_fairness"]["score"]) == c["if_score"]
+    assert float(m["individual_fairness"]["details"]["std_similarity"]) == c["if_std"]
+    assert float(m["equal_opportunity"]["score"]) == c["eo_score"]
+    assert [[k, float(v)] for k, v in m["equal_opportunity"]["details"]["opportunity_by_group"].items()] == c["eo_by_group"]
