@@ -138,14 +138,14 @@ __global__ void __launch_bounds__(COS_THREADS) cosine_kernel(const float *__rest
 // TMA-pipelined form (the fast path).  One persistent CTA per SM: a producer thread streams
 // groups of G users -- the anchor rows and the G*V counterfactual rows are each one contiguous
 // block of HBM -- into a ring of shared-memory stages with bulk TMA copies (cp.async.bulk +
-// mbarrier tx-count); eight consumer warps take batches of four rows out of the stage that
-// just landed.  HBM requests are therefore always RING bytes deep per SM (~190 KB),
+// mbarrier tx-count); sixteen consumer warps take batches of four rows out of the stage that
+// just landed (sixteen consumer warps: ncu showed the consumers, not HBM, on the critical path with eight).  HBM requests are therefore always RING bytes deep per SM (~190 KB),
 // independent of what the consumers are doing.  The arithmetic is the one described at the
 // top of this file, bit for bit: lane-strided fp64 accumulation, xor butterfly 16,8,4,2,1 --
 // the butterfly is "transposed" (eight running sums are halved at each step instead of all
 // being shuffled), which pairs exactly the same operands.
 // ---------------------------------------------------------------------------------------
-constexpr int TMA_CONSUMER_WARPS = 8;
+constexpr int TMA_CONSUMER_WARPS = 16;
 constexpr int TMA_THREADS = (TMA_CONSUMER_WARPS + 1) * 32;
 constexpr int TMA_MAX_STAGES = 4;
 
@@ -207,7 +207,8 @@ __device__ __forceinline__ float reduce_batch_scores(const double (&x)[8], const
     return score_from(dot, my_na, nb);
 }
 
-// FAST: D == NC * 128 (no partial chunk) and one user per stage -- the benchmark shape.
+// FAST: D == NC * 128 (no partial chunk) and batches of four rows that never straddle two users --
+// the benchmark shape (two users per stage, sixteen batches, one per consumer warp).
 template <int NC, bool FAST>
 __global__ void __launch_bounds__(TMA_THREADS, 1) cosine_tma_kernel(const CosTmaParams p) {
     extern __shared__ __align__(128) unsigned char smem[];
@@ -265,30 +266,37 @@ __global__ void __launch_bounds__(TMA_THREADS, 1) cosine_tma_kernel(const CosTma
             double av[NC][4];
             double na = 0.0;
             if constexpr (FAST) {
-                const int rows = V;
-                const int n_batches = (rows + 3) >> 2;
-                {   // the stage's single anchor row, kept as fp64 for the whole stage
-                    double acc = 0.0;
-#pragma unroll
-                    for (int c = 0; c < NC; ++c) {
-                        const float4 q = *reinterpret_cast<const float4 *>(sa + 4 * (lane + 32 * c));
-                        av[c][0] = q.x; av[c][1] = q.y; av[c][2] = q.z; av[c][3] = q.w;
-#pragma unroll
-                        for (int e = 0; e < 4; ++e) acc = fma(av[c][e], av[c][e], acc);
-                    }
-                    na = warp_sum(acc);
-                }
+                // batches never straddle users: user slot = batch / pub, rows (batch % pub) * 4 .. + 3
+                const int nu = static_cast<int>(min(static_cast<int64_t>(G), p.U - u0));
+                const int pub = (V + 3) >> 2;                  // batches per user
+                const int n_batches = nu * pub;
+                int cur_slot = -1;
                 for (int batch = first; batch < n_batches; batch += TMA_CONSUMER_WARPS) {
-                    const int r0 = batch * 4;
+                    const int slot = batch / pub;
+                    const int r0 = (batch - slot * pub) * 4;
+                    if (slot != cur_slot) {                    // warp-uniform: this user's anchor row as fp64
+                        const float *arow = sa + static_cast<size_t>(slot) * D;
+                        double acc = 0.0;
+#pragma unroll
+                        for (int c = 0; c < NC; ++c) {
+                            const float4 q = *reinterpret_cast<const float4 *>(arow + 4 * (lane + 32 * c));
+                            av[c][0] = q.x; av[c][1] = q.y; av[c][2] = q.z; av[c][3] = q.w;
+#pragma unroll
+                            for (int e = 0; e < 4; ++e) acc = fma(av[c][e], av[c][e], acc);
+                        }
+                        na = warp_sum(acc);
+                        cur_slot = slot;
+                    }
+                    const float *srow = sb + static_cast<size_t>(slot) * V * D;
                     double x[8];
                     const double na_row[4] = {na, na, na, na};
-                    if (r0 + 4 <= rows) {                      // full batch: twelve independent 128-bit loads
+                    if (r0 + 4 <= V) {                         // full batch: twelve independent 128-bit loads
                         float4 q[4][NC];
 #pragma unroll
                         for (int i = 0; i < 4; ++i)
 #pragma unroll
                             for (int c = 0; c < NC; ++c)
-                                q[i][c] = *reinterpret_cast<const float4 *>(sb + static_cast<size_t>(r0 + i) * D + 4 * (lane + 32 * c));
+                                q[i][c] = *reinterpret_cast<const float4 *>(srow + static_cast<size_t>(r0 + i) * D + 4 * (lane + 32 * c));
 #pragma unroll
                         for (int i = 0; i < 4; ++i) {
                             double d = 0.0, n = 0.0;
@@ -300,18 +308,18 @@ __global__ void __launch_bounds__(TMA_THREADS, 1) cosine_tma_kernel(const CosTma
 #pragma unroll
                         for (int i = 0; i < 4; ++i) {
                             double d = 0.0, n = 0.0;
-                            if (r0 + i < rows) {
+                            if (r0 + i < V) {
 #pragma unroll
                                 for (int c = 0; c < NC; ++c)
-                                    fma4(av[c], *reinterpret_cast<const float4 *>(sb + static_cast<size_t>(r0 + i) * D + 4 * (lane + 32 * c)), d, n);
+                                    fma4(av[c], *reinterpret_cast<const float4 *>(srow + static_cast<size_t>(r0 + i) * D + 4 * (lane + 32 * c)), d, n);
                             }
                             x[2 * i] = d; x[2 * i + 1] = n;
                         }
                     }
                     const float sc = reduce_batch_scores(x, na_row, lane);
                     const int r = r0 + (lane >> 3);
-                    if ((lane & 7) == 0 && r < rows) {
-                        p.out[u0 * V + r] = sc;
+                    if ((lane & 7) == 0 && r < V) {
+                        p.out[(u0 + slot) * V + r] = sc;
                         if (do_hist) atomicAdd(&s_hist[select_key::key_f32(sc) >> 21], 1u);
                     }
                 }
@@ -381,8 +389,9 @@ bool launch_cos_tma(const float *a, const float *b, int64_t U, int V, int D, flo
     const size_t user_bytes = static_cast<size_t>(V + 1) * D * 4;
     const size_t budget = 200 * 1024;                        // ring bytes per SM
     if (user_bytes * 2 > budget) return false;               // fewer than two stages would fit
+    // users per stage: enough rows to give every consumer warp a batch, at most half the ring per stage
     int G = 1;
-    while ((G + 1) * user_bytes <= 50 * 1024 && (G * V) < 4 * TMA_CONSUMER_WARPS) ++G;
+    while ((G + 1) * user_bytes <= budget / 2 && (G * ((V + 3) / 4)) < TMA_CONSUMER_WARPS) ++G;
     CosTmaParams p{};
     p.a = a; p.b = b; p.U = U; p.V = V; p.D = D; p.G = G; p.out = out;
     p.hist0 = reinterpret_cast<unsigned long long *>(hist0);
@@ -393,7 +402,7 @@ bool launch_cos_tma(const float *a, const float *b, int64_t U, int V, int D, flo
     const size_t smem = 128 + FLR_SELECT_BINS * 4 + static_cast<size_t>(p.stages) * p.stage_bytes;
     const int64_t n_groups = (U + G - 1) / G;
     const int grid = static_cast<int>(std::min<int64_t>(n_groups, device_sm_count()));
-    const bool fast = (G == 1) && (D == NC * 128);
+    const bool fast = (D == NC * 128);
     auto kern = fast ? cosine_tma_kernel<NC, true> : cosine_tma_kernel<NC, false>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
     if (e != cudaSuccess) {
