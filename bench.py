@@ -35,7 +35,7 @@ FALLBACK_HBM_GBS = 6650.0          # /opt/skills/guides/B200_PROFILING.md fallba
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=50)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--users-per-gpu", type=int, default=1_250_000)
@@ -84,13 +84,16 @@ class ClockSampler:
         while not self._stop.is_set():
             try:
                 self.samples.append(int(self.nv.nvmlDeviceGetClockInfo(self.h, self.nv.NVML_CLOCK_SM)))
+            except Exception:
+                pass
+            try:
                 mask = int(self.nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h))
                 for bit, name in self.REASONS.items():
                     if mask & bit:
                         self.reasons.add(name)
             except Exception:
                 pass
-            time.sleep(0.01)
+            time.sleep(0.005)
 
     def start(self):
         if self.ok:
