@@ -202,6 +202,16 @@ def other_configs(dev, peak):
     out["cfg2_phase1_metrics_6040x31_k20"] = {
         "pairs": 6040 * 31, "ms_l2_flushed": ms_cold, "ms_l2_warm": ms_warm, "pairs_per_s": 6040 * 31 / (ms_cold * 1e-3),
         "note": "15 MB working set: bounded by launch + tile latency, not HBM (SURVEY.md section 7)"}
+    del neutral, nlen, lists, lens
+    # the same K = 20 shape at a size that is HBM-resident, not L2-resident (1M users, 3.2 GB of lists)
+    Ub = 1_000_000
+    neutral, nlen, lists, lens = ops.synth_lists(pipeline.SEED, 0, Ub, 31, 20, 3706, dev)
+    ms_big = timed(lambda: ops.list_metrics(neutral, nlen, lists, lens, vocab=3706), reps=5)
+    k20_bytes = Ub * 31 * (20 * 4 * 32 / 31 + 4 * 32 / 31 + 16)
+    out["list_metrics_k20_1M_users"] = {
+        "pairs": Ub * 31, "ms": ms_big, "pairs_per_s": Ub * 31 / (ms_big * 1e-3), "gbs": k20_bytes / (ms_big * 1e-3) / 1e9,
+        "frac_of_measured_hbm": k20_bytes / (ms_big * 1e-3) / 1e9 / peak}
+    del neutral, nlen, lists, lens
     # configs[2]: 1M calibration pairs of 384-d fp32 embeddings: cosine + exact quantile + violations
     N = 1_000_000
     ea, eb = ops.synth_embeddings(pipeline.SEED, 0, N, 1, 384, dev)
