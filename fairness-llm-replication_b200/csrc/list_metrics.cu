@@ -289,8 +289,7 @@ __global__ void __launch_bounds__(NT, 2) list_metrics_reg_kernel(const LmParams 
     int32_t *s_na = reinterpret_cast<int32_t *>(smem + L.off_na);
     uint8_t *s_tab = smem + L.off_tab;
     uint32_t *s_bits = reinterpret_cast<uint32_t *>(smem + L.off_bits);
-    int32_t *s_keep = reinterpret_cast<int32_t *>(smem + L.total);          // [T][KT] neutral ids of the live tile
-    int32_t *s_keep_len = s_keep + p.T * KT;                                  // [T]
+    int32_t *s_keep = reinterpret_cast<int32_t *>(smem + L.total);          // [T][KT] neutral ids of the live tile (vocab = none)
     double *s_recip = reinterpret_cast<double *>(smem + L.total + align16(static_cast<size_t>(p.T) * (KT * 4 + 4)));  // [2 KT + 1]
 
     constexpr int VEC = (KT % 4 == 0) ? 4 : 2;
