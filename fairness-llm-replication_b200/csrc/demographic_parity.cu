@@ -47,21 +47,38 @@ __global__ void __launch_bounds__(GH_THREADS) group_item_histogram_kernel(
         const int len = r >= 0 ? max(0, min(min(lens[r], K), k_cap)) : 0;
         const int max_len = __reduce_max_sync(0xffffffffu, len);
         const int32_t *row = lists + (r >= 0 ? r : 0) * K;
-        for (int j = 0; j < max_len; ++j) {
-            int id = -1;
-            if (j < len) {
-                id = row[j];
-                if (static_cast<unsigned>(id) >= static_cast<unsigned>(vocab)) id = -1;
-            }
-            // Popular titles dominate (Zipf): ids 0..31 are counted with six ballots -- lane L keeps the
-            // running count of id L in a register -- and only the long tail goes to shared-memory
-            // atomics, where two lanes rarely meet.  (MATCH.ANY-based merging measured 3x slower.)
-            const bool hot = static_cast<unsigned>(id) < 32u;
-            unsigned m = __ballot_sync(0xffffffffu, hot);
+        // a lane's row is contiguous: fetch it in chunks of CH ids with independent loads (one exposed
+        // memory latency per chunk instead of one per id), then vote on the chunk out of registers
+        constexpr int CH = 16;
+        const bool vec2 = (K % 2 == 0) && ((reinterpret_cast<uintptr_t>(lists) & 7u) == 0);
+        for (int j0 = 0; j0 < max_len; j0 += CH) {
+            int buf[CH];
+            if (vec2 && j0 + CH <= K) {
 #pragma unroll
-            for (int b = 0; b < 5; ++b) m &= __ballot_sync(0xffffffffu, (id >> b) & 1) ^ inv[b];
-            hot_cnt += __popc(m);
-            if (id >= 32) atomicAdd(&s_cnt[id], 1u);
+                for (int e = 0; e < CH; e += 2) {
+                    int2 q = make_int2(-1, -1);
+                    if (j0 + e < len) q = *reinterpret_cast<const int2 *>(row + j0 + e);
+                    buf[e] = q.x; buf[e + 1] = q.y;
+                }
+            } else {
+#pragma unroll
+                for (int e = 0; e < CH; ++e) buf[e] = (j0 + e < len) ? row[j0 + e] : -1;
+            }
+#pragma unroll
+            for (int e = 0; e < CH; ++e) {
+                if (j0 + e >= max_len) break;                      // warp-uniform
+                int id = (j0 + e < len) ? buf[e] : -1;
+                if (static_cast<unsigned>(id) >= static_cast<unsigned>(vocab)) id = -1;
+                // Popular titles dominate (Zipf): ids 0..31 are counted with six ballots -- lane L keeps the
+                // running count of id L in a register -- and only the long tail goes to shared-memory
+                // atomics, where two lanes rarely meet.  (MATCH.ANY-based merging measured 3x slower.)
+                const bool hot = static_cast<unsigned>(id) < 32u;
+                unsigned m = __ballot_sync(0xffffffffu, hot);
+#pragma unroll
+                for (int b = 0; b < 5; ++b) m &= __ballot_sync(0xffffffffu, (id >> b) & 1) ^ inv[b];
+                hot_cnt += __popc(m);
+                if (id >= 32) atomicAdd(&s_cnt[id], 1u);
+            }
         }
     }
     if (hot_cnt && (threadIdx.x & 31) < vocab) atomicAdd(&s_cnt[threadIdx.x & 31], hot_cnt);
