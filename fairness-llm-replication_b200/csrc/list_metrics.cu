@@ -267,8 +267,8 @@ __global__ void __launch_bounds__(NT, 2) list_metrics_table_kernel(const LmParam
 }
 
 // ---------------------------------------------------------------------------------------
-// Register kernel: the table kernel specialised for a compile-time row length KT (the
-// benchmark shapes K = 10, 20, 50).  Same data structures and results; what changes is the
+// Register kernel: the table kernel with a compile-time row capacity KT in {10, 20, 32, 50, 62}; a
+// row of K <= KT ids is padded with the spare id (K = 10, 20, 50 -- the benchmark shapes -- are exact).  Same data structures and results; what changes is the
 // schedule:
 //   * each thread copies its row from the staged tile into registers and the CTA immediately
 //     re-arms the bulk TMA copy of its NEXT tile into the same buffer, so the HBM read of tile
@@ -280,7 +280,8 @@ __global__ void __launch_bounds__(NT, 2) list_metrics_table_kernel(const LmParam
 template <int KT, bool RANK>
 __global__ void __launch_bounds__(NT, 2) list_metrics_reg_kernel(const LmParams p) {
     extern __shared__ __align__(16) unsigned char smem[];
-    const LmSmem L = lm_layout(p.T, p.V, KT, p.vocab_pad, p.W);
+    const int K = p.K;                                   // row length in memory, K <= KT (the unroll capacity)
+    const LmSmem L = lm_layout(p.T, p.V, K, p.vocab_pad, p.W);
     uint64_t *bar = reinterpret_cast<uint64_t *>(smem);
     int32_t *s_lists = reinterpret_cast<int32_t *>(smem + L.off_lists);
     int32_t *s_neutral = reinterpret_cast<int32_t *>(smem + L.off_neutral);
@@ -317,14 +318,14 @@ __global__ void __launch_bounds__(NT, 2) list_metrics_reg_kernel(const LmParams 
     __syncthreads();
 
     const int64_t n_tiles = (p.U + T - 1) / T;
-    const uint32_t bytes_lists = static_cast<uint32_t>(T) * V * KT * 4, bytes_neutral = static_cast<uint32_t>(T) * KT * 4;
+    const uint32_t bytes_lists = static_cast<uint32_t>(T) * V * K * 4, bytes_neutral = static_cast<uint32_t>(T) * K * 4;
     const uint32_t bytes_lens = static_cast<uint32_t>(T) * V * 4, bytes_nlen = static_cast<uint32_t>(T) * 4;
     auto issue_tma = [&](int64_t tile) {       // thread 0 only; the stage buffer must be free
         const int64_t u0 = tile * T;
         fence_proxy_async();
         mbar_expect_tx(bar, bytes_lists + bytes_neutral + bytes_lens + bytes_nlen);
-        bulk_g2s(s_lists, p.lists + u0 * V * KT, bytes_lists, bar);
-        bulk_g2s(s_neutral, p.neutral + u0 * KT, bytes_neutral, bar);
+        bulk_g2s(s_lists, p.lists + u0 * V * K, bytes_lists, bar);
+        bulk_g2s(s_neutral, p.neutral + u0 * K, bytes_neutral, bar);
         bulk_g2s(s_lens, p.lens + u0 * V, bytes_lens, bar);
         bulk_g2s(s_nlen, p.neutral_len + u0, bytes_nlen, bar);
     };
@@ -344,10 +345,10 @@ __global__ void __launch_bounds__(NT, 2) list_metrics_reg_kernel(const LmParams 
             mbar_wait(bar, phase);
             phase ^= 1u;
         } else {
-            const int32_t *gl = p.lists + u0 * V * KT;
-            for (int i = t; i < tu * V * KT; i += NT) s_lists[i] = gl[i];
-            const int32_t *gn = p.neutral + u0 * KT;
-            for (int i = t; i < tu * KT; i += NT) s_neutral[i] = gn[i];
+            const int32_t *gl = p.lists + u0 * V * K;
+            for (int i = t; i < tu * V * K; i += NT) s_lists[i] = gl[i];
+            const int32_t *gn = p.neutral + u0 * K;
+            for (int i = t; i < tu * K; i += NT) s_neutral[i] = gn[i];
             for (int i = t; i < tu * V; i += NT) s_lens[i] = p.lens[u0 * V + i];
             for (int i = t; i < tu; i += NT) s_nlen[i] = p.neutral_len[u0 + i];
             __syncthreads();
@@ -355,22 +356,27 @@ __global__ void __launch_bounds__(NT, 2) list_metrics_reg_kernel(const LmParams 
 
         // ---- move the tile out of the stage buffer: own row -> registers, neutral lists -> s_keep ----
         unsigned ids[KT];
-        int Kb = KT;
+        int Kb = K;
         const bool live = pair_thread && slot < tu;
         if (live) {
             Kb = max(0, min(s_lens[t], Kn));
-            const int32_t *row = s_lists + t * KT;
+            const int32_t *row = s_lists + t * K;
+            if (K == KT) {                                   // warp-uniform: vector loads of the whole row
 #pragma unroll
-            for (int j0 = 0; j0 < KT; j0 += VEC) {
-                int tmp[VEC];
-                load_ids<VEC>(row + j0, tmp);
+                for (int j0 = 0; j0 < KT; j0 += VEC) {
+                    int tmp[VEC];
+                    load_ids<VEC>(row + j0, tmp);
 #pragma unroll
-                for (int e = 0; e < VEC; ++e) ids[j0 + e] = static_cast<unsigned>(tmp[e]);
+                    for (int e = 0; e < VEC; ++e) ids[j0 + e] = static_cast<unsigned>(tmp[e]);
+                }
+            } else {                                         // shorter rows in memory: positions >= K are spare
+#pragma unroll
+                for (int j = 0; j < KT; ++j) ids[j] = j < K ? static_cast<unsigned>(row[j]) : vocab;
             }
         }
         // Rows shorter than KT are rare: only a warp that holds one pays for masking the tail.  A
         // masked position holds the id `vocab`, the spare element (see the main loop).
-        if (__any_sync(0xffffffffu, Kb < KT)) {
+        if (__any_sync(0xffffffffu, Kb < K)) {
 #pragma unroll
             for (int j = 0; j < KT; ++j)
                 if (j >= Kb) ids[j] = vocab;
@@ -380,7 +386,7 @@ __global__ void __launch_bounds__(NT, 2) list_metrics_reg_kernel(const LmParams 
         //      need no barrier between them; the ids are parked in s_keep for the un-mark. ----
         for (int s = warp; s < tu; s += NT / 32) {
             const int Ka = max(0, min(s_nlen[s], Kn));
-            const int32_t *A = s_neutral + s * KT;
+            const int32_t *A = s_neutral + s * K;
             uint8_t *tab = s_tab + s * p.vocab_pad;
             const unsigned id0 = lane < Ka ? static_cast<unsigned>(A[lane]) : vocab;
             const unsigned id1 = lane + 32 < Ka ? static_cast<unsigned>(A[lane + 32]) : vocab;
@@ -457,7 +463,7 @@ __global__ void __launch_bounds__(NT, 2) list_metrics_reg_kernel(const LmParams 
                 int spare_hits = 0;
 #pragma unroll
                 for (int j = 0; j < KT; ++j) spare_hits += ids[j] >= vocab ? 1 : 0;
-                oov += spare_hits - (KT - Kb);
+                oov += spare_hits - (KT - Kb);                      // positions >= Kb all hold the spare id
             }
             const int n_a = s_na[slot];
             const int uni = n_a + n_b - inter;
@@ -638,7 +644,7 @@ __global__ void __launch_bounds__(256) list_metrics_cmp_finalize_kernel(const do
 
 struct Plan {
     bool table;        // table / register kernel (else compare kernel)
-    int reg_k;         // compile-time row length of the register kernel, 0 = generic table kernel
+    int reg_k;         // unroll capacity of the register kernel (>= K), 0 = generic table kernel (K = 63, 64)
     int T, vocab_pad, W, grid;
     size_t smem;
     int64_t cmp_threads;
@@ -651,11 +657,12 @@ Plan make_plan(int64_t U, int V, int K, int k_cap, int vocab) {
     pl.W = (vocab + 31) / 32;
     pl.table = false;
     if (vocab > 0 && vocab <= 16384 && k_cap <= FLR_MAX_RANK_K && V >= 2 && V <= NT) {
-        const bool reg = (K == 10 || K == 20 || K == 50);
+        const int cap = K <= 10 ? 10 : K <= 20 ? 20 : K <= 32 ? 32 : K <= 50 ? 50 : K <= 62 ? 62 : 0;   // unroll capacity
+        const bool reg = cap != 0;
         // register kernel extras: neutral ids + lengths of the live tile, and the reciprocal table
         auto bytes = [&](int T) {
             return lm_layout(T, V, K, pl.vocab_pad, pl.W).total +
-                   (reg ? align16(static_cast<size_t>(T) * (K * 4 + 4)) + align16((2 * K + 1) * sizeof(double)) : 0);
+                   (reg ? align16(static_cast<size_t>(T) * (cap * 4 + 4)) + align16((2 * cap + 1) * sizeof(double)) : 0);
         };
         int T = NT / V;
         if (T >= 4) T &= ~3;                 // multiples of 4 keep every bulk copy 16-byte sized
@@ -663,7 +670,7 @@ Plan make_plan(int64_t U, int V, int K, int k_cap, int vocab) {
             T = (T > 4) ? ((T - 1) & ~3) : T - 1;
         if (T >= 1 && T * V * 2 >= NT) {      // at least half of the CTA's threads own a pair
             pl.table = true;
-            pl.reg_k = reg ? K : 0;
+            pl.reg_k = cap;
             pl.T = T;
             pl.smem = bytes(T);
             const int64_t tiles = (U + T - 1) / T;
@@ -692,7 +699,9 @@ TableKernel pick_table_kernel(const Plan &pl, int K, bool rank) {
     switch (pl.reg_k) {
         case 10: return rank ? list_metrics_reg_kernel<10, true> : list_metrics_reg_kernel<10, false>;
         case 20: return rank ? list_metrics_reg_kernel<20, true> : list_metrics_reg_kernel<20, false>;
+        case 32: return rank ? list_metrics_reg_kernel<32, true> : list_metrics_reg_kernel<32, false>;
         case 50: return rank ? list_metrics_reg_kernel<50, true> : list_metrics_reg_kernel<50, false>;
+        case 62: return rank ? list_metrics_reg_kernel<62, true> : list_metrics_reg_kernel<62, false>;
         default: break;
     }
     const int vec = (K % 4 == 0) ? 4 : (K % 2 == 0) ? 2 : 1;
