@@ -48,6 +48,8 @@ SIGNATURES = {
     "flr_group_item_histogram": (_i32, [_vp, _vp, _vp, _i64, _i32, _i32, _i32, _i32, _vp, _vp]),
     "flr_js_distance_matrix": (_i32, [_vp, _i32, _i32, _vp, _vp, _vp]),
     "flr_equal_opportunity_counts": (_i32, [_vp, _vp, _i32, _i32, _vp, _vp, _vp]),
+    "flr_ndcg": (_i32, [_vp, _vp, _i32, _vp, _vp, _i32, _i32, _vp, _i64, _vp, _vp]),
+    "flr_exposure_by_group": (_i32, [_vp, _vp, _i32, _i32, _vp, _i64, _vp, _vp, _vp]),
     "flr_normalize_rows_bf16": (_i32, [_vp, _i64, _i32, _vp, _vp]),
     "flr_pair_similarity_scratch_bytes": (_sz, [_i64, _i32, _i32]),
     "flr_pair_similarity_gemm": (_i32, [_vp, _i64, _i32, _i32, _vp, _vp, _sz, _vp]),

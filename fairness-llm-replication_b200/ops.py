@@ -20,7 +20,7 @@ from ._lib import (DTYPE_F32, DTYPE_F64, EMPTY_ANY_IS_ZERO, EMPTY_BOTH_IS_ONE, M
 __all__ = [
     "list_metrics", "ListMetrics", "pair_jaccard", "cosine_nonconformity", "radix_select",
     "threshold_schedule", "violation_detect", "conformal_keep_len", "normalize_rows_bf16",
-    "pair_similarity", "group_item_histogram", "js_distance_matrix", "equal_opportunity_counts", "synth_lists", "synth_embeddings", "synth_lists_host",
+    "pair_similarity", "group_item_histogram", "js_distance_matrix", "equal_opportunity_counts", "ndcg", "exposure_by_group", "synth_lists", "synth_embeddings", "synth_lists_host",
     "synth_embeddings_host", "zipf_cdf_host", "device_info",
     "EMPTY_ANY_IS_ZERO", "EMPTY_BOTH_IS_ONE",
 ]
@@ -294,6 +294,40 @@ def equal_opportunity_counts(hist, relevant):
     tot = torch.zeros(G, dtype=torch.int64, device=hist.device)
     _lib.call("flr_equal_opportunity_counts", _ptr(hist), _ptr(relevant), G, vocab, _ptr(rel), _ptr(tot), _stream())
     return rel, tot
+
+
+# ------------------------------------------------------------------------------ ranking metrics (phase 2)
+def ndcg(rel, rel_len, ideal, ideal_len, k: int) -> torch.Tensor:
+    """NDCG@k of B rankings (src/utils.py:113-132): rel float64 [B, n] relevances in rank order, ideal
+    float64 [B, m] ground-truth relevances sorted descending; returns float64 [B]."""
+    rel = _dev(rel, torch.float64, "rel")
+    ideal = _dev(ideal, torch.float64, "ideal")
+    rel_len = _dev(rel_len, torch.int32, "rel_len")
+    ideal_len = _dev(ideal_len, torch.int32, "ideal_len")
+    B, n = rel.shape
+    m = ideal.shape[1]
+    log2tab = torch.from_numpy(np.log2(np.arange(max(n, m, 1)) + 2)).to(rel.device)      # the reference's np.log2
+    out = torch.empty(B, dtype=torch.float64, device=rel.device)
+    _lib.call("flr_ndcg", _ptr(rel), _ptr(rel_len), n, _ptr(ideal), _ptr(ideal_len), m, int(k), _ptr(log2tab), B,
+              _ptr(out), _stream())
+    torch.cuda.current_stream().synchronize()         # log2tab is released on return
+    return out
+
+
+def exposure_by_group(group, lens, n_groups: int):
+    """Mean exposure 1/log2(pos + 2) per protected group for B rankings
+    (src/phase2_cross_model_eval.py:228-243): group uint8 [B, n] (255 = skip); returns
+    (float64 [B, G] means, int32 [B, G] counts)."""
+    group = _dev(group, torch.uint8, "group")
+    lens = _dev(lens, torch.int32, "lens")
+    B, n = group.shape
+    weight = torch.from_numpy(1.0 / np.log2(np.arange(n) + 2)).to(group.device)          # the reference's expression
+    mean = torch.empty((B, n_groups), dtype=torch.float64, device=group.device)
+    cnt = torch.empty((B, n_groups), dtype=torch.int32, device=group.device)
+    _lib.call("flr_exposure_by_group", _ptr(group), _ptr(lens), n, int(n_groups), _ptr(weight), B, _ptr(mean), _ptr(cnt),
+              _stream())
+    torch.cuda.current_stream().synchronize()         # weight is released on return
+    return mean, cnt
 
 
 # ------------------------------------------------------------------------------ config 4

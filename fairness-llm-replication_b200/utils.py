@@ -184,3 +184,53 @@ def calculate_equal_opportunity(recommendations_by_group: Dict[str, List[List[st
     variance = np.var(scores) if scores else 0
     fairness_score = 1 / (1 + variance)
     return fairness_score, opportunity_scores
+
+
+def _exposure_means(groups_in_rank_order: Sequence[Hashable]):
+    """(group names in order of first appearance, {name: np.float64 mean exposure}) on the GPU."""
+    names: List[Hashable] = []
+    code: Dict[Hashable, int] = {}
+    ids = []
+    for g in groups_in_rank_order:
+        if g not in code:
+            code[g] = len(names)
+            names.append(g)
+        ids.append(code[g])
+    if not ids:
+        return names, {}
+    if len(ids) > 128 or len(names) > 255:
+        raise ValueError("exposure ratio: at most 128 ranked items and 255 groups on the GPU path")
+    dev = _device()
+    mean, _ = ops.exposure_by_group(torch.tensor([ids], dtype=torch.uint8, device=dev),
+                                    torch.tensor([len(ids)], dtype=torch.int32, device=dev), len(names))
+    vals = mean.cpu().numpy()[0]
+    return names, {name: vals[i] for i, name in enumerate(names)}
+
+
+def calculate_exposure_ratio(rankings: List[Tuple[str, str]], protected_attribute: str = 'gender') -> Tuple[float, Dict[str, float]]:
+    """Exposure ratio of a ranking of (item, group) tuples -- reference: src/utils.py:277-305: exposure
+    1/log2(position + 2), mean per group, min/max of the means (1.0 when there is nothing to compare)."""
+    _, avg_exposure = _exposure_means([group for _, group in rankings])
+    if not avg_exposure:
+        return 1.0, {}
+    max_exposure = max(avg_exposure.values())
+    min_exposure = min(avg_exposure.values())
+    exposure_ratio = min_exposure / max_exposure if max_exposure > 0 else 1.0
+    return exposure_ratio, avg_exposure
+
+
+def calculate_ndcg(rankings: List[str], ground_truth: Dict[str, float], k: int = 10) -> float:
+    """NDCG@k -- reference: src/utils.py:113-132 (missing items count 0; IDCG from the k largest
+    ground-truth values; 0.0 when IDCG is 0).  Bit-identical: same additions in the same order."""
+    rel = [float(ground_truth.get(item, 0)) for item in rankings[:k]]
+    ideal = [float(v) for v in sorted(ground_truth.values(), reverse=True)[:k]]
+    if not ideal:
+        return 0.0                       # IDCG is 0
+    dev = _device()
+    n = max(len(rel), 1)
+    out = ops.ndcg(torch.tensor([rel + [0.0] * (n - len(rel))], dtype=torch.float64, device=dev),
+                   torch.tensor([len(rel)], dtype=torch.int32, device=dev),
+                   torch.tensor([ideal], dtype=torch.float64, device=dev),
+                   torch.tensor([len(ideal)], dtype=torch.int32, device=dev), 1 << 30)   # already cut to k
+    v = float(out.cpu().numpy()[0])
+    return v if v != 0.0 else 0.0

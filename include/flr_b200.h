@@ -210,6 +210,26 @@ int flr_equal_opportunity_counts(const uint64_t *hist, const uint8_t *relevant, 
                                  uint64_t *out_relevant, uint64_t *out_total, void *stream);
 
 /* ---------------------------------------------------------------------------------------
+ * Ranking-fairness metrics of phase 2, batched over B rankings.
+ * flr_ndcg replaces the loops of utils.calculate_ndcg (src/utils.py:118-132): rel double [B, n] =
+ * relevance of the ranked items in rank order, ideal double [B, m] = the ground-truth relevances
+ * sorted descending, log2tab[i] = log2(i + 2) (from the caller, so it is the reference's own
+ * transcendental); out[b] = DCG@k / IDCG@k, 0 when IDCG is 0.  Sums run left to right as in the
+ * reference: the result is bit-identical.
+ * flr_exposure_by_group replaces the per-group exposure means of calculate_exposure_ratio
+ * (src/phase2_cross_model_eval.py:228-243, src/utils.py:286-296): group uint8 [B, n] = protected
+ * group of the item at each rank (255 = item unknown, skipped), weight[pos] = 1 / log2(pos + 2);
+ * out_mean double [B, G] = numpy-order mean of the group's exposures (0 when it has none), out_cnt
+ * int32 [B, G].  n <= 128.
+ * ------------------------------------------------------------------------------------- */
+int flr_ndcg(const double *rel, const int32_t *rel_len, int n, const double *ideal,
+             const int32_t *ideal_len, int m, int k, const double *log2tab, int64_t B,
+             double *out, void *stream);
+int flr_exposure_by_group(const uint8_t *group, const int32_t *len, int n, int n_groups,
+                          const double *weight, int64_t B, double *out_mean, int32_t *out_cnt,
+                          void *stream);
+
+/* ---------------------------------------------------------------------------------------
  * Dense per-user similarity matrices S[u] = X[u] X[u]^T (config 4; no reference code).
  *   x bf16 [U, M, D] (rows L2-normalised by flr_normalize_rows_bf16), out float [U, M, M].
  *   tcgen05.mma (kind::f16, fp32 accumulate in TMEM), operands staged by TMA.

@@ -245,6 +245,40 @@ def main():
                                "if_score": float(ifs), "if_std": float(ifd["std_similarity"]), "eo_score": float(eos),
                                "eo_by_group": [[k, float(v)] for k, v in eod["opportunity_by_group"].items()]}
 
+    # ---- N3: ranking metrics of phase 2 (src/phase2_cross_model_eval.py:216-316, src/utils.py:113,277) ----
+    p2 = ref_loader.load("phase2_cross_model_eval")
+    cases = []
+    for _ in range(10):
+        n = rng.randint(1, 24)
+        items = [{"id": f"i{j}", "protected_attribute": rng.choice(["male", "female", "other"]),
+                  "relevance_score": round(rng.random(), 3)} for j in range(n)]
+        if rng.random() < 0.3:
+            del items[0]["relevance_score"]
+        if rng.random() < 0.3:
+            del items[-1]["protected_attribute"]
+        ranked = [it["id"] for it in items]
+        rng.shuffle(ranked)
+        if rng.random() < 0.5:
+            ranked.insert(rng.randint(0, len(ranked)), "ghost")             # an id the model made up
+        ratio, avg = p2.calculate_exposure_ratio(ranked, items)
+        k = rng.choice([3, 5, 10, 50])
+        nd = p2.calculate_ndcg_per_group(ranked, items, k)
+        tuples = [(it["id"], it.get("protected_attribute", "unknown")) for it in items]
+        r2, avg2 = utils.calculate_exposure_ratio(tuples)
+        gt = {it["id"]: it.get("relevance_score", 0.5) for it in items}
+        cases.append({"ranked": ranked, "items": items, "k": k, "ratio": float(ratio),
+                      "avg": [[a, float(b)] for a, b in avg.items()], "ndcg_per_group": [[a, float(b)] for a, b in nd.items()],
+                      "tuples": [list(t) for t in tuples], "ratio_tuples": float(r2),
+                      "avg_tuples": [[a, float(b)] for a, b in avg2.items()],
+                      "ndcg_all": float(utils.calculate_ndcg(ranked, gt, k))})
+    comps = [{"winner": rng.choice(["A", "B", "tie"]), "item_a_attr": rng.choice(["m", "f"]), "item_b_attr": rng.choice(["m", "f"])}
+             for _ in range(25)]
+    g["ranking_metrics"] = {"cases": cases, "comparisons": comps,
+                            "win_rates": [[a, float(b)] for a, b in p2.calculate_pairwise_preference_ratio(comps).items()],
+                            "ndcg_known": float(utils.calculate_ndcg(["i2", "i1", "i3"], {"i1": 5, "i2": 3, "i3": 1})),
+                            "ndcg_empty": float(utils.calculate_ndcg(["a"], {})),
+                            "exposure_empty": float(p2.calculate_exposure_ratio([], [])[0])}
+
     with open(OUT, "w") as f:
         json.dump(g, f, indent=0, sort_keys=True)
     print("wrote", OUT, os.path.getsize(OUT), "bytes")

@@ -201,3 +201,44 @@ def calculate_equal_opportunity(recommendations_by_group, relevant_items):
         scores[group] = len(set(flat) & set(relevant_items)) / len(flat) if flat else 0.0
     vals = list(scores.values())
     return 1 / (1 + (np.var(vals) if vals else 0)), scores
+
+
+def calculate_ndcg(rankings, ground_truth, k=10):
+    """src/utils.py:113-132 -- DCG@k / IDCG@k with rel / log2(i + 2), missing items 0, 0.0 when IDCG is 0."""
+    dcg = 0.0
+    for i, item in enumerate(rankings[:k]):
+        dcg += ground_truth.get(item, 0) / np.log2(i + 2)
+    idcg = sum(rel / np.log2(i + 2) for i, rel in enumerate(sorted(ground_truth.values(), reverse=True)[:k]))
+    return 0.0 if idcg == 0 else dcg / idcg
+
+
+def exposure_ratio_from_groups(groups_in_rank_order):
+    """Shared core of src/utils.py:277-305 and src/phase2_cross_model_eval.py:216-254: exposure
+    1/log2(pos + 2) (None = position without a known item), np.mean per group, min/max."""
+    by_group = {}
+    for pos, g in enumerate(groups_in_rank_order):
+        if g is not None:
+            by_group.setdefault(g, []).append(1.0 / np.log2(pos + 2))
+    return {g: np.mean(v) for g, v in by_group.items()}
+
+
+def calculate_exposure_ratio_p2(ranked_items, items_data, protected_attr="protected_attribute"):
+    """src/phase2_cross_model_eval.py:216-254."""
+    lookup = {it["id"]: it for it in items_data}
+    avg = exposure_ratio_from_groups([lookup[i].get(protected_attr, "unknown") if i in lookup else None
+                                      for i in ranked_items])
+    if len(avg) < 2:
+        return 1.0, avg
+    return (min(avg.values()) / max(avg.values()) if max(avg.values()) > 0 else 1.0), avg
+
+
+def calculate_ndcg_per_group(ranked_items, items_data, k=10):
+    """src/phase2_cross_model_eval.py:281-316."""
+    by_group = {}
+    for it in items_data:
+        by_group.setdefault(it.get("protected_attribute", "unknown"), []).append(it)
+    out = {}
+    for g, items in by_group.items():
+        gt = {it["id"]: it.get("relevance_score", 0.5) for it in items}
+        out[g] = calculate_ndcg([i for i in ranked_items if i in gt], gt, k)
+    return out

@@ -248,3 +248,17 @@ def test_equal_opportunity_port(golden):
         score, by_group = R.calculate_equal_opportunity(dict(c["groups"]), set(c["relevant"]))
         assert [[k, float(v)] for k, v in by_group.items()] == c["by_group"]
         assert float(score) == c["score"]
+
+
+def test_ranking_metrics_port(golden):
+    rm = golden["ranking_metrics"]
+    assert rm["ndcg_known"] == 0.9001539923801699
+    assert R.calculate_ndcg(["i2", "i1", "i3"], {"i1": 5, "i2": 3, "i3": 1}) == rm["ndcg_known"]
+    assert R.calculate_ndcg(["a"], {}) == rm["ndcg_empty"] == 0.0
+    for c in rm["cases"]:
+        ratio, avg = R.calculate_exposure_ratio_p2(c["ranked"], c["items"])
+        assert float(ratio) == c["ratio"] and [[a, float(b)] for a, b in avg.items()] == c["avg"]
+        nd = R.calculate_ndcg_per_group(c["ranked"], c["items"], c["k"])
+        assert [[a, float(b)] for a, b in nd.items()] == c["ndcg_per_group"]
+        gt = {it["id"]: it.get("relevance_score", 0.5) for it in c["items"]}
+        assert float(R.calculate_ndcg(c["ranked"], gt, c["k"])) == c["ndcg_all"]
