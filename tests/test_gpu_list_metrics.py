@@ -348,3 +348,30 @@ def test_phase1_metric_step_on_a_results_file(golden, tmp_path):
     assert float(m["individual_fairness"]["details"]["std_similarity"]) == c["if_std"]
     assert float(m["equal_opportunity"]["score"]) == c["eo_score"]
     assert [[k, float(v)] for k, v in m["equal_opportunity"]["details"]["opportunity_by_group"].items()] == c["eo_by_group"]
+
+
+def test_dropin_edge_inputs_match_the_port():
+    """Inputs the golden file does not hold: very long lists (Jaccard-only compare kernel), non-ASCII and
+    near-identical titles, non-string items, the same list object on both sides."""
+    from fairness_llm_replication_b200 import utils, phase3_final as fin
+    from fairness_llm_replication_b200 import phase3_facter_mitigation as p3
+    from oracle import ref_port as R
+    rng = np.random.default_rng(8)
+    long_a = [f"title {i}" for i in rng.integers(0, 900, 300)]
+    long_b = [f"title {i}" for i in rng.integers(0, 900, 412)]
+    shared = ["Amélie", "Amelie", "amelie ", "千と千尋の神隠し", "", " ", "Se7en", "Se7en"]
+    recs = {"a": long_a, "b": long_b, "c": shared, "d": list(reversed(shared)), "e": [1, 2.0, (3, 4), None, 1],
+            "f": [2, None, "1"], "g": shared}
+    pairs = [("a", "b"), ("b", "a"), ("c", "d"), ("c", "g"), ("e", "f"), ("a", "c"), ("g", "g")]
+    got = utils.calculate_individual_fairness(pairs, recs)
+    want = R.calculate_individual_fairness(pairs, recs)
+    assert got[1] == want[1] and float(got[0]) == float(want[0])
+    assert fin.jaccard(set(long_a), set(long_b)) == R.jaccard(set(long_a), set(long_b))
+    q = p3.measure_quality_preservation({"u": long_a, "v": {"recommendations": shared}}, {"u": long_b, "v": shared})
+    w = R.measure_quality_preservation({"u": long_a, "v": {"recommendations": shared}}, {"u": long_b, "v": shared})
+    assert float(q["average_overlap"]) == float(w["average_overlap"]) and q["num_comparisons"] == w["num_comparisons"]
+    d = {"g1": [long_a, shared], "g2": [long_b, shared[:3]], "g3": [["x"]]}
+    s_got, det = utils.calculate_demographic_parity(d)
+    s_want, det_w = R.calculate_demographic_parity(d)
+    assert det["distributions"] == det_w["distributions"]
+    assert det["divergences"] == pytest.approx(det_w["divergences"], rel=1e-12)
