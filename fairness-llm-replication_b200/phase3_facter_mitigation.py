@@ -75,7 +75,7 @@ def calculate_conformal_thresholds(calibration_data: pd.DataFrame, alpha: float 
         calibration_data["group"]           # same KeyError as the reference on a column-less frame
         return thresholds
     codes, uniques = pd.factorize(calibration_data["group"], use_na_sentinel=True)
-    scores = np.ascontiguousarray(calibration_data["nonconformity"].values, dtype=np.float64)
+    scores = np.array(calibration_data["nonconformity"].values, dtype=np.float64)      # own, writable copy
     dev = utils._device()
     t_scores = torch.from_numpy(scores).to(dev)
     names = list(uniques)
