@@ -326,6 +326,7 @@ def run_ours(args):
         d2h = res.reduced.numel() * 8 + res.thresholds.numel() * 4 + res.select_state.numel() * 8 + 4
         e2e = {"value": E * V * n_gpus * e2e_steps / dt, "unit": UNIT, "h2d_bytes_per_step": hb.nbytes(),
                "d2h_bytes_per_step": d2h, "users_per_gpu_per_step": E, "steps": e2e_steps,
+               "h2d_gbs_per_gpu": hb.nbytes() * e2e_steps / dt / 1e9,      # PCIe is the bound here (~55 GB/s on Gen5 x16)
                "note": "ScoringPipeline.run_host: chunked H2D from pinned memory overlapped with the kernels"}
         del hb
 
