@@ -74,3 +74,25 @@ def test_pipeline_repeatable():
     a = pipe.run(db)
     b = pipe.run(db)
     assert torch.equal(a.reduced, b.reduced) and torch.equal(a.flags, b.flags) and torch.equal(a.thresholds, b.thresholds)
+
+
+@pytest.mark.parametrize("K,k_cap,vocab,V", [(50, 10, 3706, 31), (20, 7, 200, 31), (30, 30, 3706, 12), (50, 50, 130, 31)])
+def test_pipeline_other_shapes(K, k_cap, vocab, V):
+    """k_cap below K, small vocabularies (many shared items, vocab just above 2K + 2), V != 31."""
+    from fairness_llm_replication_b200 import pipeline
+    cfg = pipeline.PipelineConfig(list_len=K, k_cap=k_cap, vocab=vocab, n_variants=V, emb_dim=128, rounds=3,
+                                  attribute_slices={"all": (0, V)})
+    U = 257
+    hb = pipeline.synth_batch_host(cfg, 7, U)
+    pipe = pipeline.ScoringPipeline(cfg)
+    res = pipe.run(pipeline.Batch(*[t.cuda() for t in hb.tensors()]))
+    summ = pipe.summarize(res)
+    lm, scores, v = _oracle_pipeline(cfg, hb)
+    assert np.array_equal(res.inter.cpu().numpy(), lm["inter"])
+    np.testing.assert_allclose(res.serp.cpu().numpy(), lm["serp"], rtol=1e-6)
+    np.testing.assert_allclose(res.prag.cpu().numpy(), lm["prag"], rtol=1e-6)
+    assert np.array_equal(res.scores.cpu().numpy(), scores)
+    assert np.array_equal(res.thresholds.cpu().numpy(), v["thresholds"])
+    assert np.array_equal(res.flags.cpu().numpy(), v["flags"])
+    np.testing.assert_allclose(summ["variant_means"][:, 2], lm["prag"].mean(0), rtol=1e-12)
+    assert set(summ["spreads"]) == {"all"}
