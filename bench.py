@@ -40,7 +40,9 @@ def parse_args():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--users-per-gpu", type=int, default=1_250_000)
     ap.add_argument("--e2e-users", type=int, default=65_536)
-    ap.add_argument("--cpu-sample-users", type=int, default=4096)
+    ap.add_argument("--cpu-sample-users", type=int, default=16384, help="users per CPU-arm batch")
+    ap.add_argument("--cpu-sample-seconds", type=float, default=10.0,
+                    help="cpu_baseline keeps scoring batches until this much scoring time has accumulated")
     ap.add_argument("--list-len", type=int, default=50)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
@@ -144,7 +146,7 @@ def run_reference(args):
         return
     cfg = workload_config(args, args.gpus)
     steps, warm = max(1, args.steps), max(0, args.warmup)
-    # bounded: about 1-2 s of CPU work per step
+    # bounded: about 0.5-1 s of scoring (all host cores) per step
     n = args.cpu_sample_users
     for _ in range(min(warm, 1)):
         cpu_sample(args, min(n, 512))
@@ -350,9 +352,15 @@ def run_ours(args):
                               "peak_source": peak_src, "frac_of_nominal_8000": ach / 8000.0}
         cpu = None
         if n_gpus == 1 and not args.no_cpu_baseline:
-            v, dt, cores = cpu_sample(args, args.cpu_sample_users)
-            cpu = {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
-                   "sample": "%d users x 31 variants, full pipeline, %.1f s" % (args.cpu_sample_users, dt)}
+            # bounded sample: batches of --cpu-sample-users users until about 10 s of scoring time
+            n, t_sum, reps, cores = args.cpu_sample_users, 0.0, 0, 1
+            while t_sum < args.cpu_sample_seconds and reps < 64:
+                _, dt, cores = cpu_sample(args, n, user0=reps * n)
+                t_sum += dt
+                reps += 1
+            cpu = {"value": reps * n * V / t_sum, "unit": UNIT, "cores": cores, "kind": "port",
+                   "sample": "%d batches of %d users x %d variants, full pipeline, %.1f s of scoring on %d cores"
+                             % (reps, n, V, t_sum, cores)}
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": n_gpus, "steps": steps, "warmup": warm,
             "ms_per_step": ms_total / steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
