@@ -24,54 +24,67 @@ using namespace flr;
 namespace {
 
 // one warp per row: fp64 sum of squares (exact fp32 products), fp32 divide, RNE to bf16.
-// VEC: the row is read once with 128-bit loads and kept in registers (D % 4 == 0, D <= 1024).
-template <bool VEC>
+// NC > 0: the row is read once with 128-bit loads and kept in registers (D % 4 == 0, D <= NC * 128);
+// a warp keeps RPW rows in flight per trip so that enough bytes are outstanding per SM.  NC == 0: any D.
+template <int NC>
 __global__ void __launch_bounds__(256) normalize_rows_bf16_kernel(const float *__restrict__ x, int64_t rows, int D,
                                                                   __nv_bfloat16 *__restrict__ out) {
     const int lane = threadIdx.x & 31;
     const int64_t warp0 = static_cast<int64_t>(blockIdx.x) * 8 + (threadIdx.x >> 5);
     const int64_t nwarps = static_cast<int64_t>(gridDim.x) * 8;
-    for (int64_t r = warp0; r < rows; r += nwarps) {
-        const float *row = x + r * D;
-        double ss = 0.0;
-        if constexpr (VEC) {
-            const int nchunk = D >> 2;
-            float4 q[8];
+    if constexpr (NC > 0) {
+        constexpr int RPW = NC <= 2 ? 4 : NC <= 4 ? 2 : 1;
+        const int nchunk = D >> 2;
+        for (int64_t r0 = warp0 * RPW; r0 < rows; r0 += nwarps * RPW) {
+            float4 q[RPW][NC];
 #pragma unroll
-            for (int c = 0; c < 8; ++c) {
-                const int ch = lane + 32 * c;
-                q[c] = make_float4(0.f, 0.f, 0.f, 0.f);
-                if (ch < nchunk) q[c] = ldg_stream_f4(reinterpret_cast<const float4 *>(row) + ch);
-            }
-            // lane l sums chunks l, l+32, ... (the scalar form below strides by element instead; the two
-            // differ only in the last bits of |x|, far below bf16 resolution)
+            for (int i = 0; i < RPW; ++i) {
+                const float4 *row = reinterpret_cast<const float4 *>(x + (r0 + i) * D);
 #pragma unroll
-            for (int c = 0; c < 8; ++c) {
-                const double a = q[c].x, b2 = q[c].y, c2 = q[c].z, d2 = q[c].w;
-                ss = fma(a, a, ss); ss = fma(b2, b2, ss); ss = fma(c2, c2, ss); ss = fma(d2, d2, ss);
-            }
-#pragma unroll
-            for (int off = 16; off >= 1; off >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, off);
-            const double n = sqrt(ss);
-            const double inv = n > 0.0 ? 1.0 / n : 0.0;
-#pragma unroll
-            for (int c = 0; c < 8; ++c) {
-                const int ch = lane + 32 * c;
-                if (ch < nchunk) {
-                    // one fp64 division per row; x * (1/n) differs from x / n by < 2^-52 relative, which the
-                    // rounding to fp32 and then bf16 absorbs
-                    const float y0 = static_cast<float>(static_cast<double>(q[c].x) * inv);
-                    const float y1 = static_cast<float>(static_cast<double>(q[c].y) * inv);
-                    const float y2 = static_cast<float>(static_cast<double>(q[c].z) * inv);
-                    const float y3 = static_cast<float>(static_cast<double>(q[c].w) * inv);
-                    __nv_bfloat162 lo = __floats2bfloat162_rn(y0, y1), hi = __floats2bfloat162_rn(y2, y3);
-                    uint2 pk;
-                    pk.x = *reinterpret_cast<uint32_t *>(&lo);
-                    pk.y = *reinterpret_cast<uint32_t *>(&hi);
-                    *reinterpret_cast<uint2 *>(out + r * D + 4 * ch) = pk;
+                for (int c = 0; c < NC; ++c) {
+                    const int ch = lane + 32 * c;
+                    q[i][c] = make_float4(0.f, 0.f, 0.f, 0.f);
+                    if (r0 + i < rows && ch < nchunk) q[i][c] = ldg_stream_f4(row + ch);
                 }
             }
-        } else {
+#pragma unroll
+            for (int i = 0; i < RPW; ++i) {
+                if (r0 + i >= rows) break;           // warp-uniform
+                // lane l sums chunks l, l+32, ... (the scalar form below strides by element instead; the two
+                // differ only in the last bits of |x|, far below bf16 resolution)
+                double ss = 0.0;
+#pragma unroll
+                for (int c = 0; c < NC; ++c) {
+                    const double a = q[i][c].x, b2 = q[i][c].y, c2 = q[i][c].z, d2 = q[i][c].w;
+                    ss = fma(a, a, ss); ss = fma(b2, b2, ss); ss = fma(c2, c2, ss); ss = fma(d2, d2, ss);
+                }
+#pragma unroll
+                for (int off = 16; off >= 1; off >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, off);
+                const double n = sqrt(ss);
+                const double inv = n > 0.0 ? 1.0 / n : 0.0;
+#pragma unroll
+                for (int c = 0; c < NC; ++c) {
+                    const int ch = lane + 32 * c;
+                    if (ch < nchunk) {
+                        // one fp64 division per row; x * (1/n) differs from x / n by < 2^-52 relative, which
+                        // the rounding to fp32 and then bf16 absorbs
+                        const float y0 = static_cast<float>(static_cast<double>(q[i][c].x) * inv);
+                        const float y1 = static_cast<float>(static_cast<double>(q[i][c].y) * inv);
+                        const float y2 = static_cast<float>(static_cast<double>(q[i][c].z) * inv);
+                        const float y3 = static_cast<float>(static_cast<double>(q[i][c].w) * inv);
+                        __nv_bfloat162 lo = __floats2bfloat162_rn(y0, y1), hi = __floats2bfloat162_rn(y2, y3);
+                        uint2 pk;
+                        pk.x = *reinterpret_cast<uint32_t *>(&lo);
+                        pk.y = *reinterpret_cast<uint32_t *>(&hi);
+                        *reinterpret_cast<uint2 *>(out + (r0 + i) * D + 4 * ch) = pk;
+                    }
+                }
+            }
+        }
+    } else {
+        for (int64_t r = warp0; r < rows; r += nwarps) {
+            const float *row = x + r * D;
+            double ss = 0.0;
             for (int d = lane; d < D; d += 32) {
                 const double v = row[d];
                 ss = fma(v, v, ss);
@@ -302,12 +315,17 @@ extern "C" int flr_normalize_rows_bf16(const float *x, int64_t rows, int D, uint
     FLR_REQUIRE(x && out_bf16, FLR_E_INVALID, "normalize_rows: null pointer");
     const int grid = static_cast<int>(std::min<int64_t>((rows + 7) / 8, static_cast<int64_t>(device_sm_count()) * 8));
     const bool vec = (D % 4 == 0) && D <= 1024 && aligned16(x) && ((reinterpret_cast<uintptr_t>(out_bf16) & 7u) == 0);
-    if (vec)
-        normalize_rows_bf16_kernel<true><<<grid, 256, 0, static_cast<cudaStream_t>(stream_)>>>(
-            x, rows, D, reinterpret_cast<__nv_bfloat16 *>(out_bf16));
-    else
-        normalize_rows_bf16_kernel<false><<<grid, 256, 0, static_cast<cudaStream_t>(stream_)>>>(
-            x, rows, D, reinterpret_cast<__nv_bfloat16 *>(out_bf16));
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    __nv_bfloat16 *out = reinterpret_cast<__nv_bfloat16 *>(out_bf16);
+    switch (vec ? (D + 127) / 128 : 0) {
+        case 1: normalize_rows_bf16_kernel<1><<<grid, 256, 0, stream>>>(x, rows, D, out); break;
+        case 2: normalize_rows_bf16_kernel<2><<<grid, 256, 0, stream>>>(x, rows, D, out); break;
+        case 3: normalize_rows_bf16_kernel<3><<<grid, 256, 0, stream>>>(x, rows, D, out); break;
+        case 4: normalize_rows_bf16_kernel<4><<<grid, 256, 0, stream>>>(x, rows, D, out); break;
+        case 5: case 6: normalize_rows_bf16_kernel<6><<<grid, 256, 0, stream>>>(x, rows, D, out); break;
+        case 7: case 8: normalize_rows_bf16_kernel<8><<<grid, 256, 0, stream>>>(x, rows, D, out); break;
+        default: normalize_rows_bf16_kernel<0><<<grid, 256, 0, stream>>>(x, rows, D, out); break;
+    }
     FLR_LAUNCH_CHECK("normalize_rows_bf16_kernel");
     return FLR_OK;
 }
