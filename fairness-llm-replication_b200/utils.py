@@ -7,7 +7,10 @@ expression, so results are bit-identical to the reference's.
 """
 from __future__ import annotations
 
-from typing import Dict, Hashable, List, Optional, Sequence, Tuple
+import json
+import os
+import re
+from typing import Any, Dict, Hashable, List, Optional, Sequence, Tuple
 
 import numpy as np
 import torch
@@ -234,3 +237,37 @@ def calculate_ndcg(rankings: List[str], ground_truth: Dict[str, float], k: int =
                    torch.tensor([len(ideal)], dtype=torch.int32, device=dev), 1 << 30)   # already cut to k
     v = float(out.cpu().numpy()[0])
     return v if v != 0.0 else 0.0
+
+
+# ---- the data formats either side of the path: host text/JSON only ----
+_LEADING_NUMBER = re.compile(r'^\d+[\.\)]\s*')
+_LEADING_BULLET = re.compile(r'^[\-\*]\s*')
+_YEAR_SUFFIX = re.compile(r'\s*\(\d{4}\)')
+
+
+def load_results(filename: str, results_dir: str = '../results') -> Any:
+    """Read ``results_dir/filename`` as JSON -- reference: src/utils.py:33-49 (the reference logs and
+    re-raises; the exception a caller sees is the same FileNotFoundError / JSONDecodeError)."""
+    with open(os.path.join(results_dir, filename), 'r') as f:
+        return json.load(f)
+
+
+def parse_recommendation_list(text: str) -> List[str]:
+    """One title per non-blank line of a model reply -- reference: src/utils.py:350-375.  In this
+    order: trim, drop one leading "12." / "12)" counter, drop one leading "-" or "*" bullet, trim
+    straight quotes from both ends; a line left empty is dropped.  These strings are what the
+    string->id encoder (``encode.Vocabulary``) sees, so equality of titles is decided here."""
+    out = []
+    for raw in text.strip().split('\n'):
+        line = raw.strip()
+        if not line:
+            continue
+        line = _LEADING_BULLET.sub('', _LEADING_NUMBER.sub('', line)).strip('"\'')
+        if line:
+            out.append(line)
+    return out
+
+
+def extract_movie_title(text: str) -> str:
+    """Title without its "(1999)" year tags -- reference: src/utils.py:377-382."""
+    return _YEAR_SUFFIX.sub('', text).strip()

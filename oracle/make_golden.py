@@ -279,6 +279,21 @@ def main():
                             "ndcg_empty": float(utils.calculate_ndcg(["a"], {})),
                             "exposure_empty": float(p2.calculate_exposure_ratio([], [])[0])}
 
+    # ---- N2: text -> list of titles, the step before the string->id encoder (src/utils.py:350-382) ----
+    texts = [
+        "1. The Matrix (1999)\n2. Inception\n3) \"Toy Story (1995)\"\n",
+        "- Heat\n* 'Alien'\n\n   \n-- Up\n12.Se7en\n",
+        "",
+        "   \n\n",
+        "Here are my picks:\n1.  Fargo (1996)\n2.\tBrazil\n3. 2001: A Space Odyssey (1968)\n10) 10 Things I Hate About You",
+        "\"\"\n'\n1.\n- \n* *Stars*\n1. 2. Nested",
+        "No numbering at all\r\nSecond line\r\n",
+        "1.5 Stars\n(1999)\nMovie (19999)\nMovie (1999) (2001)  \n  Am\u00e9lie (2001)",
+    ]
+    g["text_parsing"] = [{"text": t, "lines": utils.parse_recommendation_list(t),
+                          "titles": [utils.extract_movie_title(x) for x in utils.parse_recommendation_list(t)]}
+                         for t in texts]
+
     with open(OUT, "w") as f:
         json.dump(g, f, indent=0, sort_keys=True)
     print("wrote", OUT, os.path.getsize(OUT), "bytes")

@@ -93,3 +93,19 @@ def test_ops_refuse_cpu_tensors():
     with pytest.raises(TypeError):
         ops.list_metrics(torch.zeros(2, 4, dtype=torch.int32), torch.zeros(2, dtype=torch.int32),
                          torch.zeros(2, 1, 4, dtype=torch.int32), torch.zeros(2, 1, dtype=torch.int32), vocab=8)
+
+
+def test_text_parsing_matches_reference(golden, tmp_path):
+    """N2: reply text -> titles (src/utils.py:350-382) and the JSON loader (src/utils.py:33-49)."""
+    import json
+    from fairness_llm_replication_b200 import utils
+    for c in golden["text_parsing"]:
+        lines = utils.parse_recommendation_list(c["text"])
+        assert lines == c["lines"]
+        assert [utils.extract_movie_title(x) for x in lines] == c["titles"]
+    (tmp_path / "phase1").mkdir()
+    payload = {"recommendations": {"p1": {"recommendations": ["A", "B"]}}, "n": 3}
+    (tmp_path / "phase1" / "r.json").write_text(json.dumps(payload))
+    assert utils.load_results("phase1/r.json", results_dir=str(tmp_path)) == payload
+    with pytest.raises(FileNotFoundError):
+        utils.load_results("missing.json", results_dir=str(tmp_path))
