@@ -486,18 +486,16 @@ __global__ void __launch_bounds__(NT, 2) list_metrics_reg_kernel(const LmParams 
         }
         __syncthreads();
 
-        // ---- wipe every private bit set with 128-bit stores (the row of the spare element is
-        //      re-armed in the same sweep), and un-mark the rank tables ----
+        // ---- wipe every private bit set with 128-bit stores, re-arm the spare element's word (each
+        //      thread its own: the sweep stops short of that row), and un-mark the rank tables ----
         {
             int4 *bits4 = reinterpret_cast<int4 *>(s_bits);
             const int spare_row = static_cast<int>(vocab >> 5);
-            const int spare_val = static_cast<int>(1u << (vocab & 31u));
-            const int n4 = (spare_row + 1) * (NT / 4);
-#pragma unroll 4
-            for (int i = t; i < n4; i += NT) {
-                const int v = (i / (NT / 4) == spare_row) ? spare_val : 0;
-                bits4[i] = make_int4(v, v, v, v);
-            }
+            const int n4 = spare_row * (NT / 4);
+            const int4 zero = make_int4(0, 0, 0, 0);
+#pragma unroll 8
+            for (int i = t; i < n4; i += NT) bits4[i] = zero;
+            s_bits[spare_row * NT + t] = 1u << (vocab & 31u);
         }
         for (int s = warp; s < tu; s += NT / 32) {
             const int32_t *A = s_keep + s * KT;
