@@ -439,6 +439,7 @@ __global__ void __launch_bounds__(NT, 2) list_metrics_reg_kernel(const LmParams 
                 const bool first = (w & bit) == 0u;
                 if (first) ++n_b;
                 const unsigned rr = tab[idx];                  // 63 when absent
+                __builtin_assume(rr <= 63u);                   // lets the compiler drop a mask before the 64-bit shifts
                 if constexpr (RANK) {
                     const int below = __popcll(seen2 << (rr ^ 63u));
                     if (first) prag += below;
