@@ -140,6 +140,27 @@ def cpu_sample(args, n_users, user0=0):
     return n_users * V / dt, dt, cores
 
 
+def string_api_sample(args, n_users=6452):
+    """The reference's own form of a1 (src/utils.py:217-244: string sets, one CPython thread), through
+    the oracle's string-level port on a string-decoded copy of the synthetic lists: Jaccard only."""
+    from fairness_llm_replication_b200 import ops
+    from oracle import ref_port
+    V, K = 31, args.list_len
+    neutral, nlen, lists, lens = ops.synth_lists_host(20251203, 0, n_users, V, K, 3706)
+    recs, pairs = {}, []
+    for u in range(n_users):
+        recs["u%d" % u] = ["m%d" % i for i in neutral[u, :nlen[u]]]
+        for v in range(V):
+            pid = "u%d_%d" % (u, v)
+            recs[pid] = ["m%d" % i for i in lists[u, v, :lens[u, v]]]
+            pairs.append(("u%d" % u, pid))
+    t0 = time.perf_counter()
+    ref_port.calculate_individual_fairness(pairs, recs)
+    dt = time.perf_counter() - t0
+    return {"value": len(pairs) / dt, "unit": "pairs/s (Jaccard only)", "cores": 1, "kind": "port",
+            "sample": "%d pairs of K=%d title lists, %.1f s" % (len(pairs), K, dt)}
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -361,6 +382,7 @@ def run_ours(args):
             cpu = {"value": reps * n * V / t_sum, "unit": UNIT, "cores": cores, "kind": "port",
                    "sample": "%d batches of %d users x %d variants, full pipeline, %.1f s of scoring on %d cores"
                              % (reps, n, V, t_sum, cores)}
+            cpu["string_api_single_thread"] = string_api_sample(args)
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": n_gpus, "steps": steps, "warmup": warm,
             "ms_per_step": ms_total / steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
