@@ -2,7 +2,8 @@
 // Jensen-Shannon distances between them -- utils.calculate_demographic_parity /
 // calculate_js_divergence, src/utils.py:172-215 and :89-102.
 //
-// group_item_histogram_kernel: one CTA per (group, slice of rows).  The CTA keeps the group's
+// dense_group_histogram_kernel (dense [U, V, K] layout): see the comment above it.
+// group_item_histogram_kernel (explicit group ids): one CTA per (group, slice of rows).  The CTA keeps the group's
 // `vocab` counters in shared memory.  Recommendation lists are Zipf-skewed -- most of a warp often
 // holds the same few titles -- so the 32 most popular ids are counted in registers from warp ballots
 // and only the long tail uses shared-memory atomics; non-zero counters then go to the global uint64
@@ -88,6 +89,107 @@ __global__ void __launch_bounds__(GH_THREADS) group_item_histogram_kernel(
         const unsigned int c = s_cnt[i];
         if (c) atomicAdd(h + i, static_cast<unsigned long long>(c));
     }
+}
+
+// Dense layout ([U, V, K], row r in group r % V), all V groups at once.  A persistent CTA walks a
+// contiguous range of users and keeps ALL groups' counters in shared memory as 16-bit halves of 32-bit
+// words (id x of group g lives in word g * Wd + x % Wd, half x / Wd, Wd = ceil(vocab / 2): 31 x 3706
+// counters = 224 KB).  A warp reads whole rows -- RPW = 32 / (K / VEC) rows side by side, each lane a
+// fixed (row slot, position) -- so row number, group and length cost a few instructions per row instead
+// of per item, the loads are contiguous, and the ids of a row being (almost always) distinct, the lanes
+// of a warp hit distinct counters: popular titles cost no more than rare ones.  An item that does not
+// count (past the row's length, outside the vocabulary) is added to a spare word (one per lane, never
+// read), so the loop has no branch and the idle adds do not pile onto one address.
+// A counter half holds 65535: the CTA flushes to the global uint64 histogram after every chunk of
+// 65535 / min(K, k_cap) users, which cannot add more than that to any counter.
+constexpr int DH_THREADS = 1024;
+constexpr int DH_WARPS = DH_THREADS / 32;
+constexpr size_t kDenseHistSmemBudget = 226 * 1024;
+
+__device__ __forceinline__ void dense_hist_flush(unsigned int *cnt, int V, int Wd, int vocab,
+                                                 unsigned long long *__restrict__ hist) {
+    for (int g = 0; g < V; ++g) {
+        unsigned int *c = cnt + g * Wd;
+        unsigned long long *h = hist + static_cast<size_t>(g) * vocab;
+        for (int x = threadIdx.x; x < Wd; x += DH_THREADS) {
+            const unsigned int w = c[x];
+            if (w) {
+                if (w & 0xffffu) atomicAdd(h + x, static_cast<unsigned long long>(w & 0xffffu));
+                if (w >> 16) atomicAdd(h + x + Wd, static_cast<unsigned long long>(w >> 16));
+                c[x] = 0u;
+            }
+        }
+    }
+}
+
+template <int VEC>
+__global__ void __launch_bounds__(DH_THREADS, 1) dense_group_histogram_kernel(
+    const int32_t *__restrict__ lists, const int32_t *__restrict__ lens, int64_t U, int K, int k_cap, int V,
+    int vocab, int chunk_users, unsigned long long *__restrict__ hist) {
+    extern __shared__ unsigned int cnt[];                   // [V][Wd]
+    const int Wd = (vocab + 1) >> 1;
+    const int n_words = V * Wd;
+    for (int i = threadIdx.x; i < n_words; i += DH_THREADS) cnt[i] = 0u;
+    __syncthreads();
+
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int Kv = K / VEC;                                 // vectors per row (K % VEC == 0, Kv <= 32)
+    const int RPW = 32 / Kv;                                // rows a warp reads side by side
+    const int sub = lane / Kv, pos = (lane - sub * Kv) * VEC;
+    const bool lane_used = sub < RPW;
+    const int Kc = min(K, k_cap);
+    const int pass_rows = DH_WARPS * RPW;                   // rows the CTA covers per pass
+    const int g_step = pass_rows % V;
+    const int64_t per = (U + gridDim.x - 1) / gridDim.x;
+    const int64_t ub = per * blockIdx.x, ue = min(U, ub + per);
+    constexpr int UNR = 8;                                  // passes in flight: 8 x 32 warps x 200 B per SM
+    for (int64_t uc = ub; uc < ue; uc += chunk_users) {
+        const int64_t row0 = uc * V;
+        const int n_rows = static_cast<int>(min(static_cast<int64_t>(chunk_users), ue - uc)) * V;
+        const int32_t *base = lists + row0 * K;
+        const int32_t *lbase = lens + row0;
+        int row = warp * RPW + sub;                         // chunk-relative; group of row0 is 0 (row0 = uc * V)
+        int g = row % V;
+        // running pointers (one 64-bit add per pass each) instead of an address rebuilt from offsets per load
+        const int32_t *ip = base + (static_cast<int64_t>(row) * K + pos);
+        const int32_t *lp = lbase + row;
+        const int pass_off = pass_rows * K;
+        for (; __any_sync(0xffffffffu, row < n_rows); ) {
+            int ids[UNR][VEC], wbase[UNR], len[UNR];
+#pragma unroll
+            for (int j = 0; j < UNR; ++j) {
+                const bool ok = lane_used && row < n_rows;
+                wbase[j] = g * Wd;
+                len[j] = ok ? min(__ldg(lp), Kc) : 0;
+                if constexpr (VEC == 2) {
+                    const int2 v = ok ? __ldcs(reinterpret_cast<const int2 *>(ip)) : make_int2(-1, -1);
+                    ids[j][0] = v.x; ids[j][1] = v.y;
+                } else {
+                    ids[j][0] = ok ? __ldcs(ip) : -1;
+                }
+                row += pass_rows; ip += pass_off; lp += pass_rows; g += g_step;
+                if (g >= V) g -= V;
+            }
+#pragma unroll
+            for (int j = 0; j < UNR; ++j) {
+#pragma unroll
+                for (int e = 0; e < VEC; ++e) {
+                    const unsigned id = static_cast<unsigned>(ids[j][e]);
+                    const bool counts = pos + e < len[j] && id < static_cast<unsigned>(vocab);
+                    const bool hi = id >= static_cast<unsigned>(Wd);
+                    // an item that does not count lands in a spare word past the tables (one per lane), never read
+                    const unsigned x = counts ? wbase[j] + (hi ? id - Wd : id) : static_cast<unsigned>(n_words + lane);
+                    atomicAdd(cnt + x, hi ? 0x10000u : 1u);
+                }
+            }
+        }
+        __syncthreads();
+        if (uc + chunk_users < ue) {                        // a full chunk may have filled a counter half
+            dense_hist_flush(cnt, V, Wd, vocab, hist);
+            __syncthreads();
+        }
+    }
+    dense_hist_flush(cnt, V, Wd, vocab, hist);
 }
 
 constexpr int JS_THREADS = 256;
@@ -190,6 +292,24 @@ extern "C" int flr_group_item_histogram(const int32_t *lists, const int32_t *len
                 "group_item_histogram: vocab %d does not fit the shared-memory counters (max 51200)", vocab);
     if (R == 0) return FLR_OK;
     FLR_REQUIRE(lists && lens && hist, FLR_E_INVALID, "group_item_histogram: null pointer");
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    {   // dense layout with every group's counters resident: one pass of coalesced reads
+        const size_t dense_smem = (static_cast<size_t>(n_groups) * ((vocab + 1) / 2) + 32) * sizeof(unsigned int);   // + a spare word per lane
+        const int Kc = std::min(K, k_cap);
+        const int chunk_users = 65535 / Kc;                 // a chunk adds at most 2^16 - 1 to any counter
+        const int vec = (K % 2 == 0 && (reinterpret_cast<uintptr_t>(lists) & 7u) == 0) ? 2 : 1;
+        if (!group && R % n_groups == 0 && dense_smem <= kDenseHistSmemBudget && chunk_users >= 1 && K / vec <= 32) {
+            const int64_t U = R / n_groups;
+            const int grid = static_cast<int>(std::min<int64_t>(device_sm_count(), (U + 63) / 64));
+            auto kern = vec == 2 ? dense_group_histogram_kernel<2> : dense_group_histogram_kernel<1>;
+            FLR_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                          static_cast<int>(dense_smem)));
+            kern<<<grid, DH_THREADS, dense_smem, stream>>>(lists, lens, U, K, k_cap, n_groups, vocab, chunk_users,
+                                                           reinterpret_cast<unsigned long long *>(hist));
+            FLR_LAUNCH_CHECK("dense_group_histogram_kernel");
+            return FLR_OK;
+        }
+    }
     const size_t smem = static_cast<size_t>(vocab) * sizeof(unsigned int);
     if (smem > 48 * 1024)
         FLR_CUDA(cudaFuncSetAttribute(group_item_histogram_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,

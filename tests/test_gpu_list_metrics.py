@@ -217,6 +217,44 @@ def test_repeated_runs_are_bit_identical_under_stress():
     assert int(runs[0].status.item()) == n_foreign
 
 
+def test_dense_histogram_matches_per_group_kernel_and_bincount():
+    """The all-groups-resident kernel (dense [U, V, K] layout) against the per-group kernel (explicit group
+    ids) and numpy, on rows with short lengths, foreign ids and repeats; K = 50 (one row per warp pass),
+    K = 20 (three rows side by side) and an odd K (scalar loads)."""
+    from fairness_llm_replication_b200 import ops
+    for U, V, K, vocab, k_cap in ((5003, 31, 50, 3706, None), (4001, 31, 20, 3706, 7), (1500, 7, 9, 500, None)):
+        rng = np.random.default_rng(U)
+        lists = rng.integers(-2, vocab + 40, size=(U, V, K)).astype(np.int32)
+        lists[rng.random((U, V, K)) < 0.3] = 3                                   # repeats of one popular id
+        lens = np.where(rng.random((U, V)) < 0.3, rng.integers(0, K + 1, (U, V)), K).astype(np.int32)
+        tl, tn = torch.from_numpy(lists).cuda(), torch.from_numpy(lens).cuda()
+        dense = ops.group_item_histogram(tl, tn, vocab=vocab, n_groups=V, k_cap=k_cap)
+        groups = (torch.arange(U * V, device="cuda") % V).to(torch.uint8)
+        per_group = ops.group_item_histogram(tl.view(U * V, K), tn.view(-1), vocab=vocab, n_groups=V, groups=groups,
+                                             k_cap=k_cap)
+        assert torch.equal(dense, per_group)
+        kc = K if k_cap is None else k_cap
+        live = (np.arange(K)[None, None, :] < np.minimum(lens, kc)[:, :, None]) & (lists >= 0) & (lists < vocab)
+        want = np.stack([np.bincount(lists[:, g][live[:, g]], minlength=vocab) for g in range(V)])
+        assert np.array_equal(dense.cpu().numpy(), want)
+
+
+def test_dense_histogram_counter_halves_do_not_overflow():
+    """Every position of every row holds the same id: a 16-bit counter half would wrap if the kernel did not
+    flush at its chunk boundaries (every 1310 users at K = 50; each CTA here walks 2800)."""
+    from fairness_llm_replication_b200 import ops
+    sms = ops.device_info()["sm_count"]
+    U, V, K, vocab = sms * 2800, 31, 50, 3706          # 70,000 per half per CTA without the flushes
+    lists = torch.full((U, V, K), 7, dtype=torch.int32, device="cuda")
+    lists[:, :, 1::2] = 1853 + 7                                                 # the other half of the same word
+    lens = torch.full((U, V), K, dtype=torch.int32, device="cuda")
+    h = ops.group_item_histogram(lists, lens, vocab=vocab, n_groups=V)
+    want = torch.zeros((V, vocab), dtype=torch.int64, device="cuda")
+    want[:, 7] = U * (K // 2)
+    want[:, 1860] = U * (K // 2)
+    assert torch.equal(h, want)
+
+
 # ---- string API against the reference's golden outputs ------------------------------------------
 def test_dropin_individual_fairness(golden):
     from fairness_llm_replication_b200 import utils
