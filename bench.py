@@ -127,6 +127,30 @@ def ncu_traffic(kernel, pairs):
         return None
 
 
+def bind_to_gpu_numa_node(local):
+    """Keep this rank on the CPUs next to its GPU's PCIe root, so that the pinned host buffers of the e2e
+    leg are first touched -- and therefore allocated -- on that NUMA node.  Returns a short description."""
+    try:
+        import torch
+        pr = torch.cuda.get_device_properties(local)
+        name = "%04x:%02x:%02x.0" % (pr.pci_domain_id, pr.pci_bus_id, pr.pci_device_id)
+        with open("/sys/bus/pci/devices/%s/local_cpulist" % name) as f:
+            text = f.read().strip()
+        cpus = set()
+        for part in text.split(","):
+            if part:
+                lo, _, hi = part.partition("-")
+                cpus.update(range(int(lo), int(hi or lo) + 1))
+        allowed = os.sched_getaffinity(0)
+        target = cpus & allowed
+        if target and target != allowed:
+            os.sched_setaffinity(0, target)
+            return "gpu %s: bound to %d of %d allowed cpus (%s)" % (name, len(target), len(allowed), text)
+        return "gpu %s: no narrower cpu set (local %s, allowed %d cpus)" % (name, text, len(allowed))
+    except Exception as exc:                                  # no sysfs entry, no permission: run unbound
+        return "unbound (%s)" % exc
+
+
 # ---------------------------------------------------------------------------------- CPU arm
 def cpu_sample(args, n_users, user0=0):
     """Time the oracle pipeline (oracle/cpu_pipeline.py) on a bounded sample, all host cores."""
@@ -281,6 +305,7 @@ def run_ours(args):
         raise SystemExit("bench.py needs a CUDA device: the scoring path has no CPU fallback")
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    numa = bind_to_gpu_numa_node(local)
     distributed = world > 1
     if distributed:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
@@ -350,7 +375,8 @@ def run_ours(args):
         e2e = {"value": E * V * n_gpus * e2e_steps / dt, "unit": UNIT, "h2d_bytes_per_step": hb.nbytes(),
                "d2h_bytes_per_step": d2h, "users_per_gpu_per_step": E, "steps": e2e_steps,
                "h2d_gbs_per_gpu": hb.nbytes() * e2e_steps / dt / 1e9,      # PCIe is the bound here (~55 GB/s on Gen5 x16)
-               "note": "ScoringPipeline.run_host: chunked H2D from pinned memory overlapped with the kernels"}
+               "note": "ScoringPipeline.run_host: chunked H2D from pinned memory overlapped with the kernels",
+               "cpu_binding_rank0": numa}
         del hb
 
     extra = None
