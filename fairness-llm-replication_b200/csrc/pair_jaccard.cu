@@ -20,6 +20,9 @@ constexpr int PJ_THREADS = 256;
 // renumbered into a dense per-user universe (claim a slot in a vocab-sized table with one CAS per
 // element, number the winners with a shared counter); the bit sets are then n_local bits wide
 // instead of vocab bits, which divides the popcount work by 116 / ceil(n_local / 32).
+// StageT: element type of the M x M staging matrix -- an intersection is at most K, so uint8 when K <= 255
+// (a quarter of the shared memory of int32: three CTAs per SM instead of one at M = 124, K = 20).
+template <typename StageT>
 __global__ void __launch_bounds__(PJ_THREADS) pair_jaccard_kernel(const int32_t *__restrict__ lists,
                                                                   const int32_t *__restrict__ lens, int64_t U, int M,
                                                                   int K, int vocab, int Wmax,
@@ -30,10 +33,11 @@ __global__ void __launch_bounds__(PJ_THREADS) pair_jaccard_kernel(const int32_t 
     unsigned int *s_tab = s_mem;                                           // [vocab] item -> local index
     unsigned int *s_bits = s_tab + ((vocab + 3) & ~3);                      // [M][Wp], Wp odd
     const int Wp_max = Wmax | 1;
-    int *s_inter = reinterpret_cast<int *>(s_bits + ((M * Wp_max + 3) & ~3));   // [M][M]
+    StageT *s_inter = reinterpret_cast<StageT *>(s_bits + ((M * Wp_max + 3) & ~3));   // [M][M]
     __shared__ unsigned int s_count;
     const int t = threadIdx.x;
     const int Mh = (M + 1) >> 1;                                // 2x2 blocks per side
+    const int n_blocks = Mh * (Mh + 1) / 2;                     // blocks (bm, bn) with bn >= bm
 
     for (int i = t; i < vocab; i += PJ_THREADS) s_tab[i] = EMPTY;
     for (int i = t; i < M * Wp_max; i += PJ_THREADS) s_bits[i] = 0u;
@@ -69,9 +73,13 @@ __global__ void __launch_bounds__(PJ_THREADS) pair_jaccard_kernel(const int32_t 
         }
         __syncthreads();
         // blocks (bm, bn) with bn >= bm; consecutive threads take consecutive bn
-        for (int blk = t; blk < Mh * Mh; blk += PJ_THREADS) {
-            const int bm = blk / Mh, bn = blk - bm * Mh;
-            if (bn < bm) continue;
+        for (int blk = t; blk < n_blocks; blk += PJ_THREADS) {
+            // blk-th block of the upper triangle, rows first: row bm starts at bm * Mh - bm (bm - 1) / 2
+            int bm = static_cast<int>((2.0f * Mh + 1.0f - sqrtf((2.0f * Mh + 1.0f) * (2.0f * Mh + 1.0f) - 8.0f * blk)) * 0.5f);
+            bm = min(max(bm, 0), Mh - 1);
+            while (bm > 0 && bm * Mh - bm * (bm - 1) / 2 > blk) --bm;
+            while ((bm + 1) * Mh - (bm + 1) * bm / 2 <= blk) ++bm;
+            const int bn = bm + (blk - (bm * Mh - bm * (bm - 1) / 2));
             // a block pairs rows {bm, bm+Mh} with {bn, bn+Mh}: lanes read consecutive rows (stride Wp, odd)
             const int m0 = bm, m1 = min(bm + Mh, M - 1), n0 = bn, n1 = min(bn + Mh, M - 1);
             const unsigned int *a0 = s_bits + m0 * Wp, *a1 = s_bits + m1 * Wp;
@@ -82,16 +90,18 @@ __global__ void __launch_bounds__(PJ_THREADS) pair_jaccard_kernel(const int32_t 
                 c00 += __popc(x0 & y0); c01 += __popc(x0 & y1);
                 c10 += __popc(x1 & y0); c11 += __popc(x1 & y1);
             }
-            s_inter[m0 * M + n0] = c00; s_inter[n0 * M + m0] = c00;
-            s_inter[m0 * M + n1] = c01; s_inter[n1 * M + m0] = c01;
-            s_inter[m1 * M + n0] = c10; s_inter[n0 * M + m1] = c10;
-            s_inter[m1 * M + n1] = c11; s_inter[n1 * M + m1] = c11;
+            const StageT v00 = static_cast<StageT>(c00), v01 = static_cast<StageT>(c01);
+            const StageT v10 = static_cast<StageT>(c10), v11 = static_cast<StageT>(c11);
+            s_inter[m0 * M + n0] = v00; s_inter[n0 * M + m0] = v00;
+            s_inter[m0 * M + n1] = v01; s_inter[n1 * M + m0] = v01;
+            s_inter[m1 * M + n0] = v10; s_inter[n0 * M + m1] = v10;
+            s_inter[m1 * M + n1] = v11; s_inter[n1 * M + m1] = v11;
         }
         __syncthreads();
         int32_t *dst = out_inter + u * M * M;
-        for (int i = t; i < M * M; i += PJ_THREADS) dst[i] = s_inter[i];
+        for (int i = t; i < M * M; i += PJ_THREADS) dst[i] = static_cast<int32_t>(s_inter[i]);
         if (out_sizes)
-            for (int m = t; m < M; m += PJ_THREADS) out_sizes[u * M + m] = s_inter[m * M + m];
+            for (int m = t; m < M; m += PJ_THREADS) out_sizes[u * M + m] = static_cast<int32_t>(s_inter[m * M + m]);
         // restore: forget this user's items, wipe the words that were used
         for (int i = t; i < M * K; i += PJ_THREADS) {
             const unsigned id = static_cast<unsigned>(L[i]);
@@ -113,17 +123,19 @@ extern "C" int flr_pair_jaccard(const int32_t *lists, const int32_t *lens, int64
     FLR_REQUIRE(lists && lens && out_inter, FLR_E_INVALID, "pair_jaccard: null pointer");
     // a user's M lists hold at most M*K distinct items: that bounds the dense universe
     const int Wmax = static_cast<int>((std::min<int64_t>(static_cast<int64_t>(M) * K, vocab) + 31) / 32);
-    const size_t smem = (static_cast<size_t>((vocab + 3) & ~3) + static_cast<size_t>((M * (Wmax | 1) + 3) & ~3) +
-                         static_cast<size_t>(M) * M) * 4;
+    const size_t stage_elem = K <= 255 ? 1 : K <= 65535 ? 2 : 4;
+    const size_t smem = (static_cast<size_t>((vocab + 3) & ~3) + static_cast<size_t>((M * (Wmax | 1) + 3) & ~3)) * 4 +
+                        ((static_cast<size_t>(M) * M * stage_elem + 15) & ~static_cast<size_t>(15));
     FLR_REQUIRE(smem <= 226 * 1024, FLR_E_UNSUPPORTED,
                 "pair_jaccard: M=%d lists of up to %d items over %d ids need %zu B of shared memory (max 231424)", M, K,
                 vocab, smem);
-    FLR_CUDA(cudaFuncSetAttribute(pair_jaccard_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                  static_cast<int>(smem)));
+    auto kern = stage_elem == 1 ? pair_jaccard_kernel<uint8_t>
+              : stage_elem == 2 ? pair_jaccard_kernel<uint16_t> : pair_jaccard_kernel<int32_t>;
+    FLR_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
     const int per_sm = std::max<int>(1, static_cast<int>((226 * 1024) / (smem + 1024)));
     const int grid = static_cast<int>(std::min<int64_t>(U, static_cast<int64_t>(device_sm_count()) * per_sm));
-    pair_jaccard_kernel<<<grid, PJ_THREADS, smem, static_cast<cudaStream_t>(stream_)>>>(lists, lens, U, M, K, vocab,
-                                                                                        Wmax, out_inter, out_sizes);
+    kern<<<grid, PJ_THREADS, smem, static_cast<cudaStream_t>(stream_)>>>(lists, lens, U, M, K, vocab, Wmax, out_inter,
+                                                                         out_sizes);
     FLR_LAUNCH_CHECK("pair_jaccard_kernel");
     return FLR_OK;
 }

@@ -293,8 +293,9 @@ def test_dropin_phase3_final(golden):
 def test_pair_jaccard_bitsets():
     from fairness_llm_replication_b200 import ops
     rng = np.random.default_rng(21)
-    for (U, M, K, vocab) in [(5, 124, 20, 3706), (3, 7, 5, 40), (2, 33, 50, 3706)]:
-        lists = rng.integers(0, min(vocab, 200), size=(U, M, K)).astype(np.int32)
+    # K = 300: intersections above 255 (16-bit staging); M odd: the last 2 x 2 block is clipped
+    for (U, M, K, vocab) in [(5, 124, 20, 3706), (3, 7, 5, 40), (2, 33, 50, 3706), (3, 9, 300, 1000), (301, 124, 20, 3706)]:
+        lists = rng.integers(0, min(vocab, 200 if K < 100 else 400), size=(U, M, K)).astype(np.int32)
         lens = rng.integers(0, K + 1, size=(U, M)).astype(np.int32)
         inter, sizes = ops.pair_jaccard(torch.from_numpy(lists).cuda(), torch.from_numpy(lens).cuda(), vocab=vocab)
         want = O.pair_jaccard(lists, lens)
