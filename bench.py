@@ -240,6 +240,23 @@ def other_configs(dev, peak):
         return float(np.median(ts))
 
     out = {}
+    # configs[0]: the reference's own scale -- 45 profiles, K = 10 title strings, 405 pairs -- through the
+    # string API (host encoding + one kernel launch) beside the string-level CPU port of the same function
+    from fairness_llm_replication_b200 import utils as fast_utils
+    from oracle import ref_port
+    rng = np.random.default_rng(0)
+    profiles = [{"id": "p%d" % i, "gender": g, "age": a, "occupation": o}
+                for i, (g, a, o) in enumerate((g, a, o) for g in "mfn" for a in (18, 25, 35, 45, 56) for o in ("x", "y", "z"))]
+    recs = {p_["id"]: ["Movie %d" % m for m in rng.choice(60, size=10, replace=False)] for p_ in profiles}
+    pairs = fast_utils.create_profile_pairs(profiles)
+    ours, port = [], []
+    for _ in range(7):
+        t0 = time.perf_counter(); r_ours = fast_utils.calculate_individual_fairness(pairs, recs); ours.append(time.perf_counter() - t0)
+        t0 = time.perf_counter(); r_port = ref_port.calculate_individual_fairness(pairs, recs); port.append(time.perf_counter() - t0)
+    out["cfg1_string_api_45_profiles"] = {
+        "pairs": len(pairs), "ours_ms": 1e3 * float(np.median(ours)), "cpu_port_ms": 1e3 * float(np.median(port)),
+        "identical": bool(r_ours[0] == r_port[0] and list(r_ours[1]) == list(r_port[1])),
+        "note": "wall clock incl. string->id encoding, H2D, launch, D2H; at this size the host work is all there is"}
     flush = torch.zeros(128 * 1024 * 1024, dtype=torch.float32, device=dev)
     # configs[1]: 6040 users x 31 variants, K = 20, all phase-1 metrics (15 MB: launch/latency-bound)
     cfg = pipeline.PipelineConfig(list_len=20)
