@@ -44,23 +44,51 @@ def pack_rows(rows: Sequence[Sequence[int]], k: int = 0) -> Tuple[np.ndarray, np
     return out, lens
 
 
+def _dense_codes(flat: list) -> Tuple[np.ndarray, int]:
+    """Dense int32 ids for a flat list of hashables, equal items <=> equal ids (Python ``==``/``hash``
+    semantics, as in the reference's sets).  All-string input -- the reference's case -- goes through
+    pandas' C hash table; anything else through a dict."""
+    if not flat:
+        return np.zeros(0, np.int32), 0
+    arr = np.empty(len(flat), dtype=object)
+    arr[:] = flat
+    try:
+        import pandas as pd
+        if pd.api.types.infer_dtype(arr, skipna=False) == "string":
+            codes, uniques = pd.factorize(arr, use_na_sentinel=False)
+            return codes.astype(np.int32), len(uniques)
+    except ImportError:
+        pass
+    index: Dict[Hashable, int] = {}
+    codes = np.fromiter((index.setdefault(x, len(index)) for x in flat), dtype=np.int32, count=len(flat))
+    return codes, len(index)
+
+
 def encode_pair_lists(lists_a: Sequence[Sequence[Hashable]], lists_b: Sequence[Sequence[Hashable]]):
     """Two aligned sequences of item lists -> (a [P,K], len_a [P], b [P,K], len_b [P], vocab size).
-    Lists that are the same Python object are encoded once."""
-    vocab = Vocabulary()
-    cache: Dict[int, List[int]] = {}
+    Lists that are the same Python object are encoded once; everything after the flattening is
+    vectorised (one hash pass over all items, one scatter into the padded table, two row gathers)."""
+    slot: Dict[int, int] = {}
+    order: List[Sequence[Hashable]] = []
 
-    def enc(lst):
+    def row_of(lst) -> int:
         key = id(lst)
-        r = cache.get(key)
-        if r is None:
-            r = vocab.encode(lst)
-            cache[key] = r
-        return r
+        i = slot.get(key)
+        if i is None:
+            i = len(order)
+            slot[key] = i
+            order.append(lst)
+        return i
 
-    rows_a = [enc(l) for l in lists_a]
-    rows_b = [enc(l) for l in lists_b]
-    kmax = max([len(r) for r in rows_a] + [len(r) for r in rows_b] + [1])
-    a, la = pack_rows(rows_a, kmax)
-    b, lb = pack_rows(rows_b, kmax)
-    return a, la, b, lb, max(len(vocab), 1)
+    ia = np.fromiter((row_of(l) for l in lists_a), dtype=np.int64, count=len(lists_a))
+    ib = np.fromiter((row_of(l) for l in lists_b), dtype=np.int64, count=len(lists_b))
+    lens = np.fromiter((len(l) for l in order), dtype=np.int32, count=len(order))
+    flat = [x for l in order for x in l]
+    codes, n_vocab = _dense_codes(flat)
+    K = max(int(lens.max()) if len(order) else 0, 1)
+    table = np.full((len(order), K), -1, dtype=np.int32)
+    if len(flat):
+        starts = np.cumsum(lens, dtype=np.int64) - lens
+        rows = np.repeat(np.arange(len(order), dtype=np.int64), lens)
+        table[rows, np.arange(len(flat), dtype=np.int64) - np.repeat(starts, lens)] = codes
+    return table[ia], lens[ia], table[ib], lens[ib], max(n_vocab, 1)
