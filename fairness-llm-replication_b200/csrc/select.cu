@@ -91,6 +91,75 @@ __global__ void __launch_bounds__(HIST_THREADS) select_hist_kernel(const T *__re
     }
 }
 
+// Single group, no group ids (the pipeline's global quantile): a pure stream.  Each thread reads 16-byte
+// vectors, several in flight, and feeds its matching digits through a one-entry run-length buffer --
+// neighbouring scores often share a digit in the early passes, and in the late passes almost nothing
+// matches the prefix -- so shared-memory atomics are rare and no warp-wide MATCH is needed.
+constexpr int HIST_UNR = 4;
+
+template <typename T>
+__global__ void __launch_bounds__(HIST_THREADS) select_hist_stream_kernel(const T *__restrict__ scores, int64_t N,
+                                                                          int pass,
+                                                                          const unsigned long long *__restrict__ state,
+                                                                          unsigned long long *__restrict__ hist) {
+    using K = KeyOf<T>;
+    using key_t = typename K::key_t;
+    constexpr int VEC = 16 / sizeof(T);
+    __shared__ unsigned int s_hist[FLR_SELECT_BINS];
+    const int shift = pass_shift(K::bits, pass);
+    const int nbits = pass_nbits(K::bits, pass);
+    const int hi_shift = shift + nbits;
+    const unsigned mask = (1u << nbits) - 1u;
+    for (int i = threadIdx.x; i < FLR_SELECT_BINS; i += HIST_THREADS) s_hist[i] = 0u;
+    __syncthreads();
+    bool live = true;
+    key_t want_hi = 0;
+    if (pass > 0) {
+        live = state[FLR_ST_EMPTY] == 0ull && hi_shift < K::bits;
+        want_hi = live ? static_cast<key_t>(state[FLR_ST_PREFIX]) >> hi_shift : 0;
+    }
+    int run_bin = -1;
+    unsigned run_cnt = 0;
+    auto feed = [&](T x) {
+        const key_t key = K::key(x);
+        if (pass > 0 && (key >> hi_shift) != want_hi) return;
+        const int bin = static_cast<int>((key >> shift) & mask);
+        if (bin == run_bin) { ++run_cnt; return; }
+        if (run_cnt) atomicAdd(s_hist + run_bin, run_cnt);
+        run_bin = bin; run_cnt = 1;
+    };
+    if (live) {
+        const int64_t n_vec = N / VEC;
+        const int4 *v4 = reinterpret_cast<const int4 *>(scores);
+        const int64_t stride = static_cast<int64_t>(gridDim.x) * HIST_THREADS;
+        for (int64_t i0 = static_cast<int64_t>(blockIdx.x) * HIST_THREADS + threadIdx.x; i0 < n_vec; i0 += stride * HIST_UNR) {
+            int4 q[HIST_UNR];
+#pragma unroll
+            for (int j = 0; j < HIST_UNR; ++j) {
+                const int64_t i = i0 + j * stride;
+                q[j] = i < n_vec ? __ldcs(v4 + i) : make_int4(0, 0, 0, 0);
+            }
+#pragma unroll
+            for (int j = 0; j < HIST_UNR; ++j) {
+                if (i0 + j * stride < n_vec) {
+                    const T *x = reinterpret_cast<const T *>(&q[j]);
+#pragma unroll
+                    for (int e = 0; e < VEC; ++e) feed(x[e]);
+                }
+            }
+        }
+        // the last N % VEC scores
+        const int64_t tail = n_vec * VEC + static_cast<int64_t>(blockIdx.x) * HIST_THREADS + threadIdx.x;
+        if (tail < N) feed(scores[tail]);
+        if (run_cnt) atomicAdd(s_hist + run_bin, run_cnt);
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < FLR_SELECT_BINS; i += HIST_THREADS) {
+        const unsigned int c = s_hist[i];
+        if (c) atomicAdd(hist + i, static_cast<unsigned long long>(c));
+    }
+}
+
 template <typename T>
 __global__ void __launch_bounds__(256) select_scan_kernel(int pass, int n_passes, double one_minus_alpha,
                                                           const unsigned long long *__restrict__ k_override,
@@ -179,6 +248,14 @@ int launch_hist(const void *scores, const uint8_t *group, int64_t N, int G, int 
     const int grid = static_cast<int>(std::max<int64_t>(1, std::min<int64_t>(need, static_cast<int64_t>(sms) * 8)));
     auto *st = reinterpret_cast<const unsigned long long *>(state);
     auto *hh = reinterpret_cast<unsigned long long *>(hist);
+    if (G == 1 && !group && (reinterpret_cast<uintptr_t>(scores) & 15u) == 0) {
+        const int64_t n_vec = N / (16 / sizeof(T));
+        const int64_t want = (n_vec + HIST_THREADS * HIST_UNR - 1) / (HIST_THREADS * HIST_UNR);
+        const int g2 = static_cast<int>(std::max<int64_t>(1, std::min<int64_t>(want, static_cast<int64_t>(sms) * 8)));
+        select_hist_stream_kernel<T><<<g2, HIST_THREADS, 0, stream>>>(static_cast<const T *>(scores), N, pass, st, hh);
+        FLR_LAUNCH_CHECK("select_hist_stream_kernel");
+        return FLR_OK;
+    }
     if (G <= kSmemGroups) {
         const size_t smem = static_cast<size_t>(G) * FLR_SELECT_BINS * sizeof(unsigned int);
         if (smem > 48 * 1024)

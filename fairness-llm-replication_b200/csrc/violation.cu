@@ -35,7 +35,8 @@ __global__ void __launch_bounds__(VIO_THREADS) violation_kernel(const float *__r
                                                                 const float *__restrict__ thr, int rounds,
                                                                 uint8_t *__restrict__ flags,
                                                                 unsigned long long *__restrict__ counts,
-                                                                unsigned long long *__restrict__ variant_counts) {
+                                                                unsigned long long *__restrict__ variant_counts,
+                                                                bool vec_ok) {
     extern __shared__ unsigned int s_vc[];                 // [V][rounds] when variant_counts, else [rounds]
     const int n_slots = (variant_counts ? V : 1) * rounds;
     for (int i = threadIdx.x; i < n_slots; i += VIO_THREADS) s_vc[i] = 0u;
@@ -43,44 +44,63 @@ __global__ void __launch_bounds__(VIO_THREADS) violation_kernel(const float *__r
     float q[FLR_MAX_ROUNDS];
 #pragma unroll
     for (int r = 0; r < FLR_MAX_ROUNDS; ++r) q[r] = r < rounds ? thr[r] : __int_as_float(0x7f800000);
-    unsigned int cnt[FLR_MAX_ROUNDS];
-#pragma unroll
-    for (int r = 0; r < FLR_MAX_ROUNDS; ++r) cnt[r] = 0u;
-
     const int64_t stride = static_cast<int64_t>(gridDim.x) * VIO_THREADS;
     const int64_t tid = static_cast<int64_t>(blockIdx.x) * VIO_THREADS + threadIdx.x;
-    int64_t i = tid;
-    for (; i + 3 * stride < N; i += 4 * stride) {          // four independent loads in flight
-        float s[4];
-#pragma unroll
-        for (int k = 0; k < 4; ++k) s[k] = __ldg(scores + i + k * stride);
-#pragma unroll
-        for (int k = 0; k < 4; ++k) {
-            unsigned int f = 0u;
-#pragma unroll
-            for (int r = 0; r < FLR_MAX_ROUNDS; ++r) {
-                const unsigned int hit = s[k] > q[r] ? 1u : 0u;   // q[r] = +inf beyond `rounds`; NaN never flags
-                f |= hit << r;
-                cnt[r] += hit;
-            }
-            flags[i + k * stride] = static_cast<uint8_t>(f);
-        }
-    }
-    for (; i < N; i += stride) {
-        const float s = __ldg(scores + i);
+    auto flag_of = [&](float s, unsigned int (&cnt)[FLR_MAX_ROUNDS]) {
         unsigned int f = 0u;
 #pragma unroll
         for (int r = 0; r < FLR_MAX_ROUNDS; ++r) {
-            const unsigned int hit = s > q[r] ? 1u : 0u;
+            const unsigned int hit = s > q[r] ? 1u : 0u;   // q[r] = +inf beyond `rounds`; NaN never flags
             f |= hit << r;
             cnt[r] += hit;
         }
-        flags[i] = static_cast<uint8_t>(f);
-    }
-    const int v = variant_counts ? static_cast<int>(tid % V) : 0;
+        return f;
+    };
+    auto publish = [&](int64_t first_elem, const unsigned int (&cnt)[FLR_MAX_ROUNDS]) {
+        const int v = variant_counts ? static_cast<int>(first_elem % V) : 0;
 #pragma unroll
-    for (int r = 0; r < FLR_MAX_ROUNDS; ++r)
-        if (r < rounds && cnt[r]) atomicAdd(&s_vc[v * rounds + r], cnt[r]);
+        for (int r = 0; r < FLR_MAX_ROUNDS; ++r)
+            if (r < rounds && cnt[r]) atomicAdd(&s_vc[v * rounds + r], cnt[r]);
+    };
+    // Vector path: a thread owns the elements 4 * i + k (i = tid, tid + stride, ...); 4 * stride is a
+    // multiple of V, so for each k the variant is fixed and the counts stay in registers.  One 16-byte
+    // load and one 4-byte store per four scores, four of them in flight.
+    const bool vec = vec_ok;
+    const int64_t n4 = vec ? N / 4 : 0;
+    if (vec) {
+        unsigned int cnt4[4][FLR_MAX_ROUNDS];
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+#pragma unroll
+            for (int r = 0; r < FLR_MAX_ROUNDS; ++r) cnt4[k][r] = 0u;
+        const float4 *s4 = reinterpret_cast<const float4 *>(scores);
+        uchar4 *f4 = reinterpret_cast<uchar4 *>(flags);
+        for (int64_t i = tid; i < n4; i += 4 * stride) {
+            float4 x[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) x[j] = i + j * stride < n4 ? __ldcs(s4 + i + j * stride) : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                if (i + j * stride < n4) {
+                    uchar4 o;
+                    o.x = static_cast<unsigned char>(flag_of(x[j].x, cnt4[0]));
+                    o.y = static_cast<unsigned char>(flag_of(x[j].y, cnt4[1]));
+                    o.z = static_cast<unsigned char>(flag_of(x[j].z, cnt4[2]));
+                    o.w = static_cast<unsigned char>(flag_of(x[j].w, cnt4[3]));
+                    f4[i + j * stride] = o;
+                }
+            }
+        }
+#pragma unroll
+        for (int k = 0; k < 4; ++k) publish(4 * tid + k, cnt4[k]);
+    }
+    {   // scalar path: everything when not vectorised, else the last N % 4 scores
+        unsigned int cnt[FLR_MAX_ROUNDS];
+#pragma unroll
+        for (int r = 0; r < FLR_MAX_ROUNDS; ++r) cnt[r] = 0u;
+        for (int64_t i = 4 * n4 + tid; i < N; i += stride) flags[i] = static_cast<uint8_t>(flag_of(__ldg(scores + i), cnt));
+        publish(4 * n4 + tid, cnt);
+    }
     __syncthreads();
     for (int idx = threadIdx.x; idx < n_slots; idx += VIO_THREADS) {
         const unsigned int c = s_vc[idx];
@@ -131,13 +151,14 @@ extern "C" int flr_violation_detect(const float *scores, int64_t N, int V, const
     const int sms = device_sm_count();
     int64_t blocks = std::min<int64_t>((N + VIO_THREADS - 1) / VIO_THREADS, static_cast<int64_t>(sms) * 8);
     blocks = ((blocks + V - 1) / V) * V;                   // stride % V == 0
+    const bool vec_ok = aligned16(scores) && (reinterpret_cast<uintptr_t>(flags) & 3u) == 0;
     const size_t smem = static_cast<size_t>(variant_counts ? V : 1) * rounds * sizeof(unsigned int);
     if (smem > 48 * 1024)
         FLR_CUDA(cudaFuncSetAttribute(violation_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                       static_cast<int>(smem)));
     violation_kernel<<<static_cast<unsigned>(blocks), VIO_THREADS, smem, static_cast<cudaStream_t>(stream_)>>>(
         scores, N, V, thr, rounds, flags, reinterpret_cast<unsigned long long *>(counts),
-        reinterpret_cast<unsigned long long *>(variant_counts));
+        reinterpret_cast<unsigned long long *>(variant_counts), vec_ok);
     FLR_LAUNCH_CHECK("violation_kernel");
     return FLR_OK;
 }
