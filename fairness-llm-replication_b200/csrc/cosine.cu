@@ -207,6 +207,30 @@ __device__ __forceinline__ float reduce_batch_scores(const double (&x)[8], const
     return score_from(dot, my_na, nb);
 }
 
+// Reduce four running sums over the warp with the same transposed xor butterfly (offsets 16, 8 halve the
+// set each lane carries, then 4, 2, 1): lane l ends up with sum number (l >> 3) & 3.  Every addition pairs
+// the operands the plain butterfly would, so each sum has the bits warp_sum() gives it.
+__device__ __forceinline__ double reduce4_transposed(const double (&v)[4], int lane) {
+    double y2[2], y1;
+    {
+        const bool hi = lane & 16;
+#pragma unroll
+        for (int k = 0; k < 2; ++k) {
+            const double keep = hi ? v[k + 2] : v[k], send = hi ? v[k] : v[k + 2];
+            y2[k] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
+        }
+    }
+    {
+        const bool hi = lane & 8;
+        const double keep = hi ? y2[1] : y2[0], send = hi ? y2[0] : y2[1];
+        y1 = keep + __shfl_xor_sync(0xffffffffu, send, 8);
+    }
+    y1 += __shfl_xor_sync(0xffffffffu, y1, 4);
+    y1 += __shfl_xor_sync(0xffffffffu, y1, 2);
+    y1 += __shfl_xor_sync(0xffffffffu, y1, 1);
+    return y1;
+}
+
 // FAST: D == NC * 128 (no partial chunk) and batches of four rows that never straddle two users --
 // the benchmark shape (two users per stage, sixteen batches, one per consumer warp).
 template <int NC, bool FAST>
@@ -320,6 +344,35 @@ __global__ void __launch_bounds__(TMA_THREADS, 1) cosine_tma_kernel(const CosTma
                     const int r = r0 + (lane >> 3);
                     if ((lane & 7) == 0 && r < V) {
                         p.out[(u0 + slot) * V + r] = sc;
+                        if (do_hist) atomicAdd(&s_hist[select_key::key_f32(sc) >> 21], 1u);
+                    }
+                }
+            } else if (V == 1) {
+                // calibration form (one counterfactual row per anchor): a warp takes one (a, b) pair at a time, so
+                // a 16-user stage keeps all sixteen warps busy; its three sums go through one transposed butterfly
+                const int nu = static_cast<int>(min(static_cast<int64_t>(G), p.U - u0));
+                for (int row = first; row < nu; row += TMA_CONSUMER_WARPS) {
+                    const float *arow = sa + static_cast<size_t>(row) * D, *brow = sb + static_cast<size_t>(row) * D;
+                    double acc = 0.0, d = 0.0, n = 0.0;
+#pragma unroll
+                    for (int c = 0; c < NC; ++c) {
+                        const int ch = lane + 32 * c;
+                        float4 qa = make_float4(0.f, 0.f, 0.f, 0.f), qb = qa;
+                        if (ch < nchunk) {
+                            qa = *reinterpret_cast<const float4 *>(arow + 4 * ch);
+                            qb = *reinterpret_cast<const float4 *>(brow + 4 * ch);
+                        }
+                        av[c][0] = qa.x; av[c][1] = qa.y; av[c][2] = qa.z; av[c][3] = qa.w;
+#pragma unroll
+                        for (int e = 0; e < 4; ++e) acc = fma(av[c][e], av[c][e], acc);
+                        fma4(av[c], qb, d, n);
+                    }
+                    const double v4[4] = {d, n, acc, 0.0};
+                    const double y = reduce4_transposed(v4, lane);          // lanes 0-7: dot, 8-15: |b|^2, 16-23: |a|^2
+                    const double nb_all = __shfl_sync(0xffffffffu, y, 8), na_all = __shfl_sync(0xffffffffu, y, 16);
+                    if (lane == 0) {
+                        const float sc = score_from(y, na_all, nb_all);
+                        p.out[u0 + row] = sc;
                         if (do_hist) atomicAdd(&s_hist[select_key::key_f32(sc) >> 21], 1u);
                     }
                 }

@@ -31,6 +31,9 @@ __global__ void threshold_schedule_kernel(const float *__restrict__ q0, const un
 constexpr int VIO_THREADS = 256;
 
 // grid * VIO_THREADS is a multiple of V, so thread `tid` only ever sees variant tid % V.
+// R = number of rounds, a template parameter: with the loops sized exactly the kernel is memory-bound
+// (a fixed 8-round loop made it instruction-bound at 2 TB/s).
+template <int R>
 __global__ void __launch_bounds__(VIO_THREADS) violation_kernel(const float *__restrict__ scores, int64_t N, int V,
                                                                 const float *__restrict__ thr, int rounds,
                                                                 uint8_t *__restrict__ flags,
@@ -41,26 +44,26 @@ __global__ void __launch_bounds__(VIO_THREADS) violation_kernel(const float *__r
     const int n_slots = (variant_counts ? V : 1) * rounds;
     for (int i = threadIdx.x; i < n_slots; i += VIO_THREADS) s_vc[i] = 0u;
     __syncthreads();
-    float q[FLR_MAX_ROUNDS];
+    float q[R];
 #pragma unroll
-    for (int r = 0; r < FLR_MAX_ROUNDS; ++r) q[r] = r < rounds ? thr[r] : __int_as_float(0x7f800000);
+    for (int r = 0; r < R; ++r) q[r] = thr[r];
     const int64_t stride = static_cast<int64_t>(gridDim.x) * VIO_THREADS;
     const int64_t tid = static_cast<int64_t>(blockIdx.x) * VIO_THREADS + threadIdx.x;
-    auto flag_of = [&](float s, unsigned int (&cnt)[FLR_MAX_ROUNDS]) {
+    auto flag_of = [&](float s, unsigned int (&cnt)[R]) {
         unsigned int f = 0u;
 #pragma unroll
-        for (int r = 0; r < FLR_MAX_ROUNDS; ++r) {
-            const unsigned int hit = s > q[r] ? 1u : 0u;   // q[r] = +inf beyond `rounds`; NaN never flags
+        for (int r = 0; r < R; ++r) {
+            const unsigned int hit = s > q[r] ? 1u : 0u;   // NaN never flags
             f |= hit << r;
             cnt[r] += hit;
         }
         return f;
     };
-    auto publish = [&](int64_t first_elem, const unsigned int (&cnt)[FLR_MAX_ROUNDS]) {
+    auto publish = [&](int64_t first_elem, const unsigned int (&cnt)[R]) {
         const int v = variant_counts ? static_cast<int>(first_elem % V) : 0;
 #pragma unroll
-        for (int r = 0; r < FLR_MAX_ROUNDS; ++r)
-            if (r < rounds && cnt[r]) atomicAdd(&s_vc[v * rounds + r], cnt[r]);
+        for (int r = 0; r < R; ++r)
+            if (cnt[r]) atomicAdd(&s_vc[v * rounds + r], cnt[r]);
     };
     // Vector path: a thread owns the elements 4 * i + k (i = tid, tid + stride, ...); 4 * stride is a
     // multiple of V, so for each k the variant is fixed and the counts stay in registers.  One 16-byte
@@ -68,11 +71,11 @@ __global__ void __launch_bounds__(VIO_THREADS) violation_kernel(const float *__r
     const bool vec = vec_ok;
     const int64_t n4 = vec ? N / 4 : 0;
     if (vec) {
-        unsigned int cnt4[4][FLR_MAX_ROUNDS];
+        unsigned int cnt4[4][R];
 #pragma unroll
         for (int k = 0; k < 4; ++k)
 #pragma unroll
-            for (int r = 0; r < FLR_MAX_ROUNDS; ++r) cnt4[k][r] = 0u;
+            for (int r = 0; r < R; ++r) cnt4[k][r] = 0u;
         const float4 *s4 = reinterpret_cast<const float4 *>(scores);
         uchar4 *f4 = reinterpret_cast<uchar4 *>(flags);
         for (int64_t i = tid; i < n4; i += 4 * stride) {
@@ -95,9 +98,9 @@ __global__ void __launch_bounds__(VIO_THREADS) violation_kernel(const float *__r
         for (int k = 0; k < 4; ++k) publish(4 * tid + k, cnt4[k]);
     }
     {   // scalar path: everything when not vectorised, else the last N % 4 scores
-        unsigned int cnt[FLR_MAX_ROUNDS];
+        unsigned int cnt[R];
 #pragma unroll
-        for (int r = 0; r < FLR_MAX_ROUNDS; ++r) cnt[r] = 0u;
+        for (int r = 0; r < R; ++r) cnt[r] = 0u;
         for (int64_t i = 4 * n4 + tid; i < N; i += stride) flags[i] = static_cast<uint8_t>(flag_of(__ldg(scores + i), cnt));
         publish(4 * n4 + tid, cnt);
     }
@@ -149,14 +152,21 @@ extern "C" int flr_violation_detect(const float *scores, int64_t N, int V, const
     if (N == 0) return FLR_OK;
     FLR_REQUIRE(scores && thr && flags && counts, FLR_E_INVALID, "violation_detect: null pointer");
     const int sms = device_sm_count();
-    int64_t blocks = std::min<int64_t>((N + VIO_THREADS - 1) / VIO_THREADS, static_cast<int64_t>(sms) * 8);
+    // at least 64 scores per thread when there are enough of them: the per-thread counters are published once
+    int64_t blocks = std::min<int64_t>((N + VIO_THREADS * 64 - 1) / (VIO_THREADS * 64), static_cast<int64_t>(sms) * 8);
+    blocks = std::max<int64_t>(blocks, 1);
     blocks = ((blocks + V - 1) / V) * V;                   // stride % V == 0
     const bool vec_ok = aligned16(scores) && (reinterpret_cast<uintptr_t>(flags) & 3u) == 0;
     const size_t smem = static_cast<size_t>(variant_counts ? V : 1) * rounds * sizeof(unsigned int);
+    using Kern = void (*)(const float *, int64_t, int, const float *, int, uint8_t *, unsigned long long *,
+                          unsigned long long *, bool);
+    static const Kern kernels[FLR_MAX_ROUNDS] = {violation_kernel<1>, violation_kernel<2>, violation_kernel<3>,
+                                                 violation_kernel<4>, violation_kernel<5>, violation_kernel<6>,
+                                                 violation_kernel<7>, violation_kernel<8>};
+    const Kern kern = kernels[rounds - 1];
     if (smem > 48 * 1024)
-        FLR_CUDA(cudaFuncSetAttribute(violation_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                      static_cast<int>(smem)));
-    violation_kernel<<<static_cast<unsigned>(blocks), VIO_THREADS, smem, static_cast<cudaStream_t>(stream_)>>>(
+        FLR_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+    kern<<<static_cast<unsigned>(blocks), VIO_THREADS, smem, static_cast<cudaStream_t>(stream_)>>>(
         scores, N, V, thr, rounds, flags, reinterpret_cast<unsigned long long *>(counts),
         reinterpret_cast<unsigned long long *>(variant_counts), vec_ok);
     FLR_LAUNCH_CHECK("violation_kernel");
