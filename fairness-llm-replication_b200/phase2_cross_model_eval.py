@@ -7,7 +7,6 @@ from __future__ import annotations
 from collections import defaultdict
 from typing import Dict, List, Tuple
 
-import numpy as np
 import torch
 
 from . import ops, utils

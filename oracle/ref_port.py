@@ -8,7 +8,6 @@ port because ``/root/reference`` cannot travel to the GPU box.
 """
 from __future__ import annotations
 
-import math
 from typing import Dict, List, Optional, Tuple
 
 import numpy as np

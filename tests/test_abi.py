@@ -1,6 +1,5 @@
 """The C-ABI library loads without a GPU and exports every symbol include/flr_b200.h declares;
 host-only entry points (the synthetic generator) are exercised.  No compute kernels run here."""
-import ctypes as C
 import os
 import re
 

@@ -1,7 +1,6 @@
 """Host-side logic of the drop-in layer that needs no GPU: pair enumeration, encoding,
 calibration-record generation, sharding, the pipeline's summary arithmetic."""
 import numpy as np
-import pandas as pd
 import pytest
 import torch
 
