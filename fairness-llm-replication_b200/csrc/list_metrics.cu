@@ -12,6 +12,7 @@
 // Compare kernel: vocabulary-independent O(K^2) fallback for shapes the table kernel does
 // not cover (V = 1 pair lists of the string API, huge vocabularies, K > 64 Jaccard-only).
 #include <algorithm>
+#include <cstdlib>
 #include <mutex>
 
 #include "common.cuh"
@@ -519,6 +520,329 @@ __global__ void __launch_bounds__(NT, 2) list_metrics_reg_kernel(const LmParams 
     if (oov && p.status) atomicAdd(p.status, oov);
 }
 
+// ---------------------------------------------------------------------------------------
+// Warp kernel (the fast path for 17 <= V <= 32, K <= 62): one warp per user, one lane per variant,
+// and no block-wide barrier anywhere -- every warp of a CTA runs its own pipeline over its own
+// shared-memory region (stage buffer, rank table, bit sets, mbarrier), so while one warp builds a
+// table or writes results another is in its main loop.
+//
+// Per user the warp
+//   1. waits for the bulk TMA copy of the user's V x K id block (issued one user ahead), and every
+//      lane copies its row into registers, clamping foreign ids to `vocab`; lane 0 then re-arms the
+//      copy for the warp's next user;
+//   2. builds the rank table of the neutral list (two positions per lane), t = 63 - rank, 0 = absent;
+//   3. runs the optimistic main loop.  Nearly every row is "clean": no id repeats inside it and every
+//      id lies in [0, vocab).  For a clean row every element is a first occurrence, so the exact
+//      loop's per-element conditions disappear and what is left per element is
+//        * one shared-memory atomicOr on the lane's private bit set -- it returns the old word, so
+//          "seen before" is (old & bit), OR-ed into one flag per row; unlike load -> or -> store,
+//          consecutive atomics have no ordering hazard, so a row's elements are independent
+//          (profiles/micro/smem_rmw_bench.cu measures both forms);
+//        * one byte look-up of t: the number of earlier hits ranked below is popc(seen << t)
+//          (absent: every hit), the hit's own bit is 1 << (64 - t), which is 0 for an absent item;
+//        * a multiply-add for the SERP* position sum;
+//   4. redoes flagged rows (a repeat, or a foreign id: `vocab` stands for those and its bit is always
+//      set) with the exact sequential loop -- rare, one lane at a time, from a copy of the row in
+//      shared memory;
+//   5. writes the pair's results, wipes the bit sets and un-marks the table.
+// Positions past a row's length hold spare ids (vocab + 1 + position): private bits, table entries
+// that read "absent"; each one counts as a miss that follows every hit, which is subtracted at the end.
+// ---------------------------------------------------------------------------------------
+__device__ __forceinline__ uint64_t shl64_clamped(uint64_t v, unsigned amount) {   // amount may be 64 (-> 0)
+    uint64_t r;
+    asm("shl.b64 %0, %1, %2;" : "=l"(r) : "l"(v), "r"(amount));
+    return r;
+}
+
+constexpr int WK_WARPS = NT / 32;
+
+struct WkSmem {
+    size_t off_recip, warp0, off_stage, off_tab, off_bits, off_row, warp_bytes, total;
+};
+
+__host__ __device__ inline WkSmem wk_layout(int V, int K, int KT, int vocab) {
+    WkSmem s;
+    s.off_recip = 0;
+    s.warp0 = align16((2 * KT + 1) * sizeof(double));
+    size_t o = 16;                                                    // mbarrier
+    s.off_stage = o; o = align16(o + static_cast<size_t>(V) * K * 4 + 16);     // + 16: the copy starts at a 16-byte boundary
+    s.off_tab = o;   o = align16(o + static_cast<size_t>(vocab) + 63);          // ids up to vocab + 62 are looked up
+    s.off_bits = o;  o = align16(o + (static_cast<size_t>(vocab >> 5) + 3) * 128);
+    s.off_row = o;   o = align16(o + static_cast<size_t>(KT) * 4);
+    s.warp_bytes = (o + 127) & ~static_cast<size_t>(127);
+    s.total = s.warp0 + s.warp_bytes * WK_WARPS;
+    return s;
+}
+
+template <int KT, bool RANK>
+__global__ void __launch_bounds__(NT, 2) list_metrics_warp_kernel(const LmParams p) {
+    extern __shared__ __align__(128) unsigned char smem[];
+    constexpr unsigned FULL = 0xffffffffu;
+    static_assert(KT % 2 == 0 && KT <= 62, "row length must be even; t = 63 - rank must stay >= 1");
+    const int K = p.K, V = p.V, Kn = p.k_cap;
+    const unsigned vocab = static_cast<unsigned>(p.vocab);
+    const WkSmem L = wk_layout(V, K, KT, p.vocab);
+    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    double *s_recip = reinterpret_cast<double *>(smem + L.off_recip);
+    unsigned char *wbase = smem + L.warp0 + L.warp_bytes * warp;
+    uint64_t *bar = reinterpret_cast<uint64_t *>(wbase);
+    unsigned char *s_stage = wbase + L.off_stage;
+    uint8_t *tab = wbase + L.off_tab;
+    uint32_t *s_bits = reinterpret_cast<uint32_t *>(wbase + L.off_bits);      // [word][lane]
+    uint32_t *s_row = reinterpret_cast<uint32_t *>(wbase + L.off_row);
+    const int tab_bytes16 = static_cast<int>((L.off_bits - L.off_tab) / 16);
+
+    // Id space of the private bit sets: [0, vocab) real ids; `vocab` stands for every foreign id and its
+    // bit is always set; vocab + 1 + j is the spare of row position j.  Words own_row .. own_row + 2 hold
+    // the foreign bit and the spares.
+    const unsigned spare0 = vocab + 1u;
+    const int own_row = static_cast<int>(vocab >> 5);
+    const uint32_t foreign_bit = 1u << (vocab & 31u);
+
+    for (int i = t; i <= 2 * KT; i += NT) s_recip[i] = i > 0 ? 1.0 / static_cast<double>(i) : 0.0;
+    for (int i = lane; i < tab_bytes16; i += 32) reinterpret_cast<int4 *>(tab)[i] = make_int4(0, 0, 0, 0);   // 0 = absent
+    for (int w = 0; w < own_row + 3; ++w) s_bits[w * 32 + lane] = w == own_row ? foreign_bit : 0u;
+    if (lane == 0) {
+        mbar_init(bar, 1);
+        fence_mbar_init();
+    }
+    __syncthreads();          // the only block-wide barrier: the reciprocal table is shared
+
+    const int64_t n_warps = static_cast<int64_t>(gridDim.x) * WK_WARPS;
+    const int64_t row_bytes = static_cast<int64_t>(K) * 4, user_bytes = row_bytes * V, total_bytes = user_bytes * p.U;
+    const char *lists_b = reinterpret_cast<const char *>(p.lists);
+    // bulk copy of user u's block: from the 16-byte boundary at or below it, a multiple of 16 bytes
+    auto bulk_ok = [&](int64_t u) {
+        if (!p.use_bulk || u >= p.U) return false;
+        const int64_t off = u * user_bytes, a = off & ~15LL;
+        return a + ((off - a + user_bytes + 15) & ~15LL) <= total_bytes;
+    };
+    auto issue_tma = [&](int64_t u) {          // lane 0; the stage buffer must be free
+        const int64_t off = u * user_bytes, a = off & ~15LL;
+        const uint32_t bytes = static_cast<uint32_t>((off - a + user_bytes + 15) & ~15LL);
+        fence_proxy_async();
+        mbar_expect_tx(bar, bytes);
+        bulk_g2s(s_stage, lists_b + a, bytes, bar);
+    };
+
+    const float inv_serp = 1.0f / static_cast<float>(Kn * (Kn + 1) / 2), inv_prag = 1.0f / static_cast<float>(Kn * (Kn + 1));
+    uint32_t phase = 0;
+    double acc_j = 0.0;
+    long long acc_s = 0, acc_p = 0;
+    int acc_n = 0, oov = 0;
+    const bool live = lane < V;
+
+    int64_t u = static_cast<int64_t>(blockIdx.x) * WK_WARPS + warp;
+    // the small per-user inputs travel in registers, fetched one user ahead
+    unsigned nid0 = vocab, nid1 = vocab;
+    int nlen = 0, blen = 0;
+    auto fetch_small = [&](int64_t uu, unsigned &a0, unsigned &a1, int &nl, int &bl) {
+        if (uu < p.U) {
+            const int32_t *A = p.neutral + uu * K;
+            a0 = lane < K ? static_cast<unsigned>(A[lane]) : vocab;
+            a1 = lane + 32 < K ? static_cast<unsigned>(A[lane + 32]) : vocab;
+            nl = p.neutral_len[uu];
+            bl = live ? p.lens[uu * V + lane] : 0;
+        }
+    };
+    fetch_small(u, nid0, nid1, nlen, blen);
+    if (lane == 0 && bulk_ok(u)) issue_tma(u);
+
+    for (; u < p.U; u += n_warps) {
+        const int64_t un = u + n_warps;
+        unsigned x_id0 = vocab, x_id1 = vocab;
+        int x_nlen = 0, x_blen = 0;
+        fetch_small(un, x_id0, x_id1, x_nlen, x_blen);
+
+        // ---- stage -> registers ----
+        int delta = 0;
+        if (bulk_ok(u)) {
+            delta = static_cast<int>((u * user_bytes) & 15);
+            mbar_wait(bar, phase);
+            phase ^= 1u;
+        } else {
+            const int32_t *gl = p.lists + u * V * K;
+            for (int i = lane; i < V * K; i += 32) reinterpret_cast<int32_t *>(s_stage)[i] = gl[i];
+            __syncwarp();
+        }
+        unsigned ids[KT];
+        const int Kb = live ? max(0, min(blen, Kn)) : K;       // an idle lane redoes lane 0's row; nothing of it is kept
+        {
+            const int32_t *row = reinterpret_cast<const int32_t *>(s_stage + delta) + (live ? lane : 0) * K;
+            if (K == KT) {
+#pragma unroll
+                for (int j0 = 0; j0 < KT; j0 += 2) {
+                    const int2 q = *reinterpret_cast<const int2 *>(row + j0);
+                    ids[j0] = min(static_cast<unsigned>(q.x), vocab);
+                    ids[j0 + 1] = min(static_cast<unsigned>(q.y), vocab);
+                }
+            } else {
+#pragma unroll
+                for (int j = 0; j < KT; ++j) ids[j] = j < K ? min(static_cast<unsigned>(row[j]), vocab) : spare0 + j;
+            }
+        }
+        if (__any_sync(FULL, Kb < K)) {      // short rows are rare: only their warps mask the tail
+#pragma unroll
+            for (int j = 0; j < KT; ++j)
+                if (j >= Kb) ids[j] = spare0 + j;
+        }
+        __syncwarp();
+        if (lane == 0 && bulk_ok(un)) issue_tma(un);      // overlaps everything below
+
+        // ---- rank table: tab[id] = 63 - (first position of id in the neutral list) ----
+        int n_a;
+        {
+            const int Ka = max(0, min(nlen, Kn));
+            const unsigned id0 = lane < Ka ? nid0 : vocab, id1 = lane + 32 < Ka ? nid1 : vocab;
+            oov += (lane < Ka && id0 >= vocab ? 1 : 0) + (lane + 32 < Ka && id1 >= vocab ? 1 : 0);
+            const unsigned t0 = 63u - lane, t1 = 31u - lane;            // t of positions lane and lane + 32
+            if (id1 < vocab) tab[id1] = static_cast<uint8_t>(t1);       // later half first,
+            __syncwarp();
+            if (id0 < vocab) tab[id0] = static_cast<uint8_t>(t0);       // so the earlier half wins
+            __syncwarp();
+            bool again;
+            do {    // repeats inside one 32-wide store raced: let the first position (largest t) win, then count
+                const unsigned v0 = id0 < vocab ? tab[id0] : 255u, v1 = id1 < vocab ? tab[id1] : 255u;
+                again = false;
+                if (id0 < vocab && v0 < t0) { tab[id0] = static_cast<uint8_t>(t0); again = true; }
+                if (id1 < vocab && v1 < t1) { tab[id1] = static_cast<uint8_t>(t1); again = true; }
+                n_a = __popc(__ballot_sync(FULL, id0 < vocab && v0 == t0)) + __popc(__ballot_sync(FULL, id1 < vocab && v1 == t1));
+                again = __any_sync(FULL, again);
+                __syncwarp();
+            } while (again);
+        }
+
+        // ---- optimistic pass over the row ----
+        char *bits_base = reinterpret_cast<char *>(s_bits + lane);
+        uint32_t seen_lo = 0, seen_hi = 0;      // bit r + 1 = neutral rank r was hit
+        uint32_t repeat = 0, pos_sum = 0;
+        int prag = 0;
+#pragma unroll
+        for (int j = 0; j < KT; ++j) {
+            const unsigned idx = ids[j];                   // in [0, vocab], or a spare
+            unsigned int *wp = reinterpret_cast<unsigned int *>(bits_base + (idx & ~31u) * 4u);
+            const uint32_t bit = 1u << (idx & 31u);
+            const uint32_t old = atomicOr(wp, bit);
+            repeat |= old & bit;
+            const unsigned tt = tab[idx];                  // 63 - rank, 0 when absent
+            if constexpr (RANK) {
+                const uint64_t seen = (static_cast<uint64_t>(seen_hi) << 32) | seen_lo;
+                prag += __popcll(shl64_clamped(seen, tt));
+                pos_sum += min(tt, 1u) * static_cast<unsigned>(j);
+            }
+            const uint64_t own = shl64_clamped(1ull, 64u - tt);
+            seen_lo += static_cast<uint32_t>(own);          // bits of a clean row are distinct: + is |
+            seen_hi += static_cast<uint32_t>(own >> 32);
+        }
+        int inter = __popc(seen_lo) + __popc(seen_hi);
+        int serp = inter * Kn - static_cast<int>(pos_sum);
+        int n_b = Kb;
+        prag -= (KT - Kb) * inter;      // every spare past the row's end counted as a miss that follows all hits
+
+        // ---- flagged rows, one lane at a time: the exact loop over a copy of the row in shared memory ----
+        unsigned flagged = __ballot_sync(FULL, live && repeat != 0u);
+        while (flagged) {
+            const int owner = __ffs(flagged) - 1;
+            flagged &= flagged - 1u;
+            if (lane == owner) {
+#pragma unroll
+                for (int j = 0; j < KT; ++j) s_row[j] = ids[j];
+                for (int j = 0; j < Kb; ++j)                               // un-set what the pass above set
+                    *reinterpret_cast<uint32_t *>(bits_base + (s_row[j] & ~31u) * 4u) = 0u;
+                uint64_t seen = 0;
+                n_b = 0; inter = 0; serp = 0; prag = 0;
+                for (int j = 0; j < Kb; ++j) {
+                    const unsigned id = s_row[j];
+                    if (id >= vocab) { ++oov; continue; }
+                    uint32_t *wp = reinterpret_cast<uint32_t *>(bits_base + (id & ~31u) * 4u);
+                    const uint32_t w = *wp, bit = 1u << (id & 31u);
+                    if (w & bit) continue;
+                    *wp = w | bit;
+                    ++n_b;
+                    const unsigned tt = tab[id];
+                    if (tt != 0u) {
+                        const unsigned r = 63u - tt;
+                        ++inter;
+                        if constexpr (RANK) {
+                            serp += Kn - j;
+                            prag += __popcll(seen & ((1ull << r) - 1ull));
+                        }
+                        seen |= 1ull << r;
+                    } else if constexpr (RANK) {
+                        prag += __popcll(seen);
+                    }
+                }
+            }
+            __syncwarp();
+        }
+
+        if (live) {
+            const int uni = n_a + n_b - inter;
+            // inter * (1/uni) from a table instead of an fp64 division per pair: within one ulp of the
+            // quotient, which the fp32 output and the 1e-12 tolerance on the sums never see
+            double jac = static_cast<double>(inter) * s_recip[uni];
+            if (p.empty_policy == FLR_EMPTY_BOTH_IS_ONE) jac = uni > 0 ? jac : 1.0;
+            const int64_t pair = u * V + lane;
+            if (p.out_inter) p.out_inter[pair] = inter;
+            if (p.out_union) p.out_union[pair] = uni;
+            if (p.out_jac) p.out_jac[pair] = static_cast<float>(jac);
+            if constexpr (RANK) {
+                if (p.out_serp) p.out_serp[pair] = static_cast<float>(serp) * inv_serp;
+                if (p.out_prag) p.out_prag[pair] = static_cast<float>(prag) * inv_prag;
+            }
+            acc_j += jac;
+            acc_s += serp;
+            acc_p += prag;
+            acc_n += 1;
+        }
+
+        // ---- wipe the warp's bit sets (128-bit stores; the last three rows each lane resets itself,
+        //      re-arming the foreign bit) and un-mark the rank table ----
+        __syncwarp();
+        {
+            int4 *bits4 = reinterpret_cast<int4 *>(s_bits);
+            const int n4 = own_row * 8;
+            const int4 zero = make_int4(0, 0, 0, 0);
+#pragma unroll 8
+            for (int i = lane; i < n4; i += 32) bits4[i] = zero;
+            s_bits[own_row * 32 + lane] = foreign_bit;
+            s_bits[(own_row + 1) * 32 + lane] = 0u;
+            s_bits[(own_row + 2) * 32 + lane] = 0u;
+        }
+        if (nid0 < vocab) tab[nid0] = 0u;
+        if (nid1 < vocab) tab[nid1] = 0u;
+        __syncwarp();
+        nid0 = x_id0; nid1 = x_id1; nlen = x_nlen; blen = x_blen;
+    }
+
+    double *dst = p.partial + (static_cast<size_t>(blockIdx.x) * NT + t) * 4;
+    dst[0] = acc_j;
+    dst[1] = static_cast<double>(acc_s);
+    dst[2] = static_cast<double>(acc_p);
+    dst[3] = static_cast<double>(acc_n);
+    if (oov && p.status) atomicAdd(p.status, oov);
+}
+
+// Fixed-order reduction of the warp kernel's per-thread partials: variant v lives in lane v of every
+// warp; one warp per variant adds the (block, warp) entries l, l + 32, ... in ascending order, then an
+// xor butterfly -- the order depends only on the launch geometry.
+__global__ void __launch_bounds__(128) list_metrics_warp_finalize_kernel(const double *__restrict__ partial, int grid,
+                                                                         int V, double *__restrict__ out) {
+    const int v = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (v >= V) return;
+    double a[4] = {0, 0, 0, 0};
+    const int n = grid * WK_WARPS;
+    for (int e = lane; e < n; e += 32) {
+        const double4 q = *reinterpret_cast<const double4 *>(partial + (static_cast<size_t>(e) * 32 + v) * 4);
+        a[0] += q.x; a[1] += q.y; a[2] += q.z; a[3] += q.w;
+    }
+#pragma unroll
+    for (int off = 16; off >= 1; off >>= 1)
+#pragma unroll
+        for (int k = 0; k < 4; ++k) a[k] += __shfl_xor_sync(0xffffffffu, a[k], off);
+    if (lane == 0) { out[v * 4 + 0] = a[0]; out[v * 4 + 1] = a[1]; out[v * 4 + 2] = a[2]; out[v * 4 + 3] = a[3]; }
+}
+
 // Fixed-order reduction of the per-thread partials, one warp per variant: lane l adds the
 // (block, slot) entries l, l+32, ... in ascending order, then an xor butterfly -- the order
 // depends only on the launch geometry, so the sums are bit-reproducible.
@@ -642,8 +966,9 @@ __global__ void __launch_bounds__(256) list_metrics_cmp_finalize_kernel(const do
 }
 
 struct Plan {
-    bool table;        // table / register kernel (else compare kernel)
-    int reg_k;         // unroll capacity of the register kernel (>= K), 0 = generic table kernel (K = 63, 64)
+    bool table;        // table / register / test-and-set kernel (else compare kernel)
+    int reg_k;         // unroll capacity of the register kernels (>= K), 0 = generic table kernel (K = 63, 64)
+    bool warp;         // warp kernel (one warp per user) instead of the register kernel
     int T, vocab_pad, W, grid;
     size_t smem;
     int64_t cmp_threads;
@@ -658,6 +983,17 @@ Plan make_plan(int64_t U, int V, int K, int k_cap, int vocab) {
     if (vocab > 0 && vocab <= 16384 && k_cap <= FLR_MAX_RANK_K && V >= 2 && V <= NT) {
         const int cap = K <= 10 ? 10 : K <= 20 ? 20 : K <= 32 ? 32 : K <= 50 ? 50 : K <= 62 ? 62 : 0;   // unroll capacity
         const bool reg = cap != 0;
+        const char *pick = getenv("FLR_LM_KERNEL");
+        if (reg && V >= 17 && V <= 32 && !(pick && pick[0] == 'r')) {
+            pl.table = true;
+            pl.warp = true;
+            pl.reg_k = cap;
+            pl.T = WK_WARPS;
+            pl.smem = wk_layout(V, K, cap, vocab).total;
+            const int64_t tiles = (U + WK_WARPS - 1) / WK_WARPS;
+            pl.grid = static_cast<int>(std::min<int64_t>(std::max<int64_t>(tiles, 1), 2LL * sms));
+            return pl;
+        }
         // register kernel extras: neutral ids + lengths of the live tile, and the reciprocal table
         auto bytes = [&](int T) {
             return lm_layout(T, V, K, pl.vocab_pad, pl.W).total +
@@ -695,6 +1031,16 @@ size_t partial_bytes(const Plan &pl) {
 using TableKernel = void (*)(const LmParams);
 
 TableKernel pick_table_kernel(const Plan &pl, int K, bool rank) {
+    if (pl.warp) {
+        switch (pl.reg_k) {
+            case 10: return rank ? list_metrics_warp_kernel<10, true> : list_metrics_warp_kernel<10, false>;
+            case 20: return rank ? list_metrics_warp_kernel<20, true> : list_metrics_warp_kernel<20, false>;
+            case 32: return rank ? list_metrics_warp_kernel<32, true> : list_metrics_warp_kernel<32, false>;
+            case 50: return rank ? list_metrics_warp_kernel<50, true> : list_metrics_warp_kernel<50, false>;
+            case 62: return rank ? list_metrics_warp_kernel<62, true> : list_metrics_warp_kernel<62, false>;
+            default: break;
+        }
+    }
     switch (pl.reg_k) {
         case 10: return rank ? list_metrics_reg_kernel<10, true> : list_metrics_reg_kernel<10, false>;
         case 20: return rank ? list_metrics_reg_kernel<20, true> : list_metrics_reg_kernel<20, false>;
@@ -728,13 +1074,17 @@ int launch_planned(const Plan &pl, LmParams p, int rank_metrics, double *out_var
     p.W = pl.W;
     if (pl.table) {
         p.T = pl.T;
-        p.use_bulk = (pl.T % 4 == 0) && aligned16(p.neutral) && aligned16(p.neutral_len) && aligned16(p.lists) &&
-                     aligned16(p.lens);
+        p.use_bulk = pl.warp ? aligned16(p.lists)
+                             : (pl.T % 4 == 0) && aligned16(p.neutral) && aligned16(p.neutral_len) && aligned16(p.lists) &&
+                                   aligned16(p.lens);
         TableKernel kern = pick_table_kernel(pl, p.K, rank_metrics != 0);
         FLR_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(pl.smem)));
         kern<<<pl.grid, NT, pl.smem, stream>>>(p);
         FLR_LAUNCH_CHECK("list_metrics table/register kernel");
-        if (out_variant_sums) {
+        if (out_variant_sums && pl.warp) {
+            list_metrics_warp_finalize_kernel<<<(p.V + 3) / 4, 128, 0, stream>>>(p.partial, pl.grid, p.V, out_variant_sums);
+            FLR_LAUNCH_CHECK("list_metrics_warp_finalize_kernel");
+        } else if (out_variant_sums) {
             list_metrics_finalize_kernel<<<(p.V + 3) / 4, 128, 0, stream>>>(p.partial, pl.grid, NT, pl.T, p.V,
                                                                              out_variant_sums);
             FLR_LAUNCH_CHECK("list_metrics_finalize_kernel");
