@@ -554,6 +554,12 @@ __device__ __forceinline__ uint64_t shl64_clamped(uint64_t v, unsigned amount) {
     return r;
 }
 
+__device__ __forceinline__ uint64_t shr64_clamped(uint64_t v, unsigned amount) {   // amount may be >= 64 (-> 0)
+    uint64_t r;
+    asm("shr.b64 %0, %1, %2;" : "=l"(r) : "l"(v), "r"(amount));
+    return r;
+}
+
 constexpr int WK_WARPS = NT / 32;
 
 struct WkSmem {
@@ -578,11 +584,13 @@ template <int KT, bool RANK>
 __global__ void __launch_bounds__(NT, 2) list_metrics_warp_kernel(const LmParams p) {
     extern __shared__ __align__(128) unsigned char smem[];
     constexpr unsigned FULL = 0xffffffffu;
+    constexpr unsigned ABSENT = 64u;                     // table entry of an id that is not in the neutral list
     static_assert(KT % 2 == 0 && KT <= 62, "row length must be even; t = 63 - rank must stay >= 1");
     const int K = p.K, V = p.V, Kn = p.k_cap;
     const unsigned vocab = static_cast<unsigned>(p.vocab);
     const WkSmem L = wk_layout(V, K, KT, p.vocab);
-    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    const int t = threadIdx.x, lane = t & 31;
+    const int warp = __shfl_sync(FULL, t >> 5, 0);       // tells the compiler the value is warp-uniform
     double *s_recip = reinterpret_cast<double *>(smem + L.off_recip);
     unsigned char *wbase = smem + L.warp0 + L.warp_bytes * warp;
     uint64_t *bar = reinterpret_cast<uint64_t *>(wbase);
@@ -595,12 +603,12 @@ __global__ void __launch_bounds__(NT, 2) list_metrics_warp_kernel(const LmParams
     // Id space of the private bit sets: [0, vocab) real ids; `vocab` stands for every foreign id and its
     // bit is always set; vocab + 1 + j is the spare of row position j.  Words own_row .. own_row + 2 hold
     // the foreign bit and the spares.
-    const unsigned spare0 = vocab + 1u;
     const int own_row = static_cast<int>(vocab >> 5);
     const uint32_t foreign_bit = 1u << (vocab & 31u);
 
     for (int i = t; i <= 2 * KT; i += NT) s_recip[i] = i > 0 ? 1.0 / static_cast<double>(i) : 0.0;
-    for (int i = lane; i < tab_bytes16; i += 32) reinterpret_cast<int4 *>(tab)[i] = make_int4(0, 0, 0, 0);   // 0 = absent
+    for (int i = lane; i < tab_bytes16; i += 32)
+        reinterpret_cast<int4 *>(tab)[i] = make_int4(0x40404040, 0x40404040, 0x40404040, 0x40404040);
     for (int w = 0; w < own_row + 3; ++w) s_bits[w * 32 + lane] = w == own_row ? foreign_bit : 0u;
     if (lane == 0) {
         mbar_init(bar, 1);
@@ -609,16 +617,16 @@ __global__ void __launch_bounds__(NT, 2) list_metrics_warp_kernel(const LmParams
     __syncthreads();          // the only block-wide barrier: the reciprocal table is shared
 
     const int64_t n_warps = static_cast<int64_t>(gridDim.x) * WK_WARPS;
-    const int64_t row_bytes = static_cast<int64_t>(K) * 4, user_bytes = row_bytes * V, total_bytes = user_bytes * p.U;
+    const int64_t user_bytes = static_cast<int64_t>(K) * 4 * V, total_bytes = user_bytes * p.U;
     const char *lists_b = reinterpret_cast<const char *>(p.lists);
     // bulk copy of user u's block: from the 16-byte boundary at or below it, a multiple of 16 bytes
-    auto bulk_ok = [&](int64_t u) {
-        if (!p.use_bulk || u >= p.U) return false;
-        const int64_t off = u * user_bytes, a = off & ~15LL;
+    auto bulk_ok = [&](int64_t uu) {
+        if (!p.use_bulk || uu >= p.U) return false;
+        const int64_t off = uu * user_bytes, a = off & ~15LL;
         return a + ((off - a + user_bytes + 15) & ~15LL) <= total_bytes;
     };
-    auto issue_tma = [&](int64_t u) {          // lane 0; the stage buffer must be free
-        const int64_t off = u * user_bytes, a = off & ~15LL;
+    auto issue_tma = [&](int64_t uu) {          // lane 0; the stage buffer must be free
+        const int64_t off = uu * user_bytes, a = off & ~15LL;
         const uint32_t bytes = static_cast<uint32_t>((off - a + user_bytes + 15) & ~15LL);
         fence_proxy_async();
         mbar_expect_tx(bar, bytes);
@@ -633,7 +641,8 @@ __global__ void __launch_bounds__(NT, 2) list_metrics_warp_kernel(const LmParams
     const bool live = lane < V;
 
     int64_t u = static_cast<int64_t>(blockIdx.x) * WK_WARPS + warp;
-    // the small per-user inputs travel in registers, fetched one user ahead
+    // The small per-user inputs travel in registers, fetched one user ahead -- after the last use of the
+    // current ones, so that waiting for the current values never waits for the loads just issued.
     unsigned nid0 = vocab, nid1 = vocab;
     int nlen = 0, blen = 0;
     auto fetch_small = [&](int64_t uu, unsigned &a0, unsigned &a1, int &nl, int &bl) {
@@ -642,21 +651,20 @@ __global__ void __launch_bounds__(NT, 2) list_metrics_warp_kernel(const LmParams
             a0 = lane < K ? static_cast<unsigned>(A[lane]) : vocab;
             a1 = lane + 32 < K ? static_cast<unsigned>(A[lane + 32]) : vocab;
             nl = p.neutral_len[uu];
-            bl = live ? p.lens[uu * V + lane] : 0;
+            bl = live ? p.lens[uu * V + lane] : K;
         }
     };
     fetch_small(u, nid0, nid1, nlen, blen);
-    if (lane == 0 && bulk_ok(u)) issue_tma(u);
+    bool bulk_cur = bulk_ok(u);
+    if (lane == 0 && bulk_cur) issue_tma(u);
 
     for (; u < p.U; u += n_warps) {
         const int64_t un = u + n_warps;
-        unsigned x_id0 = vocab, x_id1 = vocab;
-        int x_nlen = 0, x_blen = 0;
-        fetch_small(un, x_id0, x_id1, x_nlen, x_blen);
+        const bool bulk_next = bulk_ok(un);
 
         // ---- stage -> registers ----
         int delta = 0;
-        if (bulk_ok(u)) {
+        if (bulk_cur) {
             delta = static_cast<int>((u * user_bytes) & 15);
             mbar_wait(bar, phase);
             phase ^= 1u;
@@ -678,18 +686,20 @@ __global__ void __launch_bounds__(NT, 2) list_metrics_warp_kernel(const LmParams
                 }
             } else {
 #pragma unroll
-                for (int j = 0; j < KT; ++j) ids[j] = j < K ? min(static_cast<unsigned>(row[j]), vocab) : spare0 + j;
+                for (int j = 0; j < KT; ++j) ids[j] = j < K ? min(static_cast<unsigned>(row[j]), vocab) : vocab + 1u + j;
             }
         }
         if (__any_sync(FULL, Kb < K)) {      // short rows are rare: only their warps mask the tail
+            unsigned spare0 = vocab + 1u;
+            asm volatile("" : "+r"(spare0));         // keeps the KT spare ids out of registers outside this block
 #pragma unroll
             for (int j = 0; j < KT; ++j)
                 if (j >= Kb) ids[j] = spare0 + j;
         }
         __syncwarp();
-        if (lane == 0 && bulk_ok(un)) issue_tma(un);      // overlaps everything below
+        if (lane == 0 && bulk_next) issue_tma(un);      // overlaps everything below
 
-        // ---- rank table: tab[id] = 63 - (first position of id in the neutral list) ----
+        // ---- rank table: tab[id] = 63 - (first position of id in the neutral list), 64 = absent ----
         int n_a;
         {
             const int Ka = max(0, min(nlen, Kn));
@@ -711,12 +721,14 @@ __global__ void __launch_bounds__(NT, 2) list_metrics_warp_kernel(const LmParams
                 __syncwarp();
             } while (again);
         }
+        const unsigned un_id0 = nid0, un_id1 = nid1;       // kept for the un-mark at the end
+        fetch_small(un, nid0, nid1, nlen, blen);            // next user's small inputs: used one iteration from now
 
         // ---- optimistic pass over the row ----
         char *bits_base = reinterpret_cast<char *>(s_bits + lane);
-        uint32_t seen_lo = 0, seen_hi = 0;      // bit r + 1 = neutral rank r was hit
-        uint32_t repeat = 0, pos_sum = 0;
-        int prag = 0;
+        uint32_t seen_lo = 0, seen_hi = 0;      // bit 63 - r = neutral rank r was hit
+        uint32_t repeat = 0, absent_pos = 0;
+        int below = 0;
 #pragma unroll
         for (int j = 0; j < KT; ++j) {
             const unsigned idx = ids[j];                   // in [0, vocab], or a spare
@@ -724,20 +736,23 @@ __global__ void __launch_bounds__(NT, 2) list_metrics_warp_kernel(const LmParams
             const uint32_t bit = 1u << (idx & 31u);
             const uint32_t old = atomicOr(wp, bit);
             repeat |= old & bit;
-            const unsigned tt = tab[idx];                  // 63 - rank, 0 when absent
+            const unsigned tt = tab[idx];                  // 63 - rank, 64 when absent
             if constexpr (RANK) {
                 const uint64_t seen = (static_cast<uint64_t>(seen_hi) << 32) | seen_lo;
-                prag += __popcll(shl64_clamped(seen, tt));
-                pos_sum += min(tt, 1u) * static_cast<unsigned>(j);
+                below += __popcll(shr64_clamped(seen, tt));         // hits so far ranked before this one (absent: 0)
+                absent_pos += (tt >> 6) * static_cast<unsigned>(j);
             }
-            const uint64_t own = shl64_clamped(1ull, 64u - tt);
-            seen_lo += static_cast<uint32_t>(own);          // bits of a clean row are distinct: + is |
+            const uint64_t own = shl64_clamped(1ull, tt);           // absent: 0
+            seen_lo += static_cast<uint32_t>(own);                  // bits of a clean row are distinct: + is |
             seen_hi += static_cast<uint32_t>(own >> 32);
         }
+        // A clean row of Kb elements with hits at positions p_1 < ... < p_h: a miss counts the hits before
+        // it, which adds up to h (Kb - 1) - sum p_i - h (h - 1) / 2; spares past the end count nothing.
         int inter = __popc(seen_lo) + __popc(seen_hi);
-        int serp = inter * Kn - static_cast<int>(pos_sum);
+        const int pos_sum = KT * (KT - 1) / 2 - static_cast<int>(absent_pos);
+        int serp = inter * Kn - pos_sum;
+        int prag = below + inter * (Kb - 1) - pos_sum - inter * (inter - 1) / 2;
         int n_b = Kb;
-        prag -= (KT - Kb) * inter;      // every spare past the row's end counted as a miss that follows all hits
 
         // ---- flagged rows, one lane at a time: the exact loop over a copy of the row in shared memory ----
         unsigned flagged = __ballot_sync(FULL, live && repeat != 0u);
@@ -760,7 +775,7 @@ __global__ void __launch_bounds__(NT, 2) list_metrics_warp_kernel(const LmParams
                     *wp = w | bit;
                     ++n_b;
                     const unsigned tt = tab[id];
-                    if (tt != 0u) {
+                    if (tt != ABSENT) {
                         const unsigned r = 63u - tt;
                         ++inter;
                         if constexpr (RANK) {
@@ -809,10 +824,10 @@ __global__ void __launch_bounds__(NT, 2) list_metrics_warp_kernel(const LmParams
             s_bits[(own_row + 1) * 32 + lane] = 0u;
             s_bits[(own_row + 2) * 32 + lane] = 0u;
         }
-        if (nid0 < vocab) tab[nid0] = 0u;
-        if (nid1 < vocab) tab[nid1] = 0u;
+        if (un_id0 < vocab) tab[un_id0] = static_cast<uint8_t>(ABSENT);
+        if (un_id1 < vocab) tab[un_id1] = static_cast<uint8_t>(ABSENT);
         __syncwarp();
-        nid0 = x_id0; nid1 = x_id1; nlen = x_nlen; blen = x_blen;
+        bulk_cur = bulk_next;
     }
 
     double *dst = p.partial + (static_cast<size_t>(blockIdx.x) * NT + t) * 4;
