@@ -754,7 +754,10 @@ __global__ void __launch_bounds__(NT, 2) list_metrics_warp_kernel(const LmParams
         int prag = below + inter * (Kb - 1) - pos_sum - inter * (inter - 1) / 2;
         int n_b = Kb;
 
-        // ---- flagged rows, one lane at a time: the exact loop over a copy of the row in shared memory ----
+        // ---- flagged rows, one at a time, redone exactly by the whole warp: the owner parks its row in
+        //      shared memory, lane l takes positions l and l + 32.  First occurrences come from a shuffle
+        //      sweep over the row; the hits ranked below an element are a prefix-OR of one-hot rank masks
+        //      over the earlier positions. ----
         unsigned flagged = __ballot_sync(FULL, live && repeat != 0u);
         while (flagged) {
             const int owner = __ffs(flagged) - 1;
@@ -762,31 +765,51 @@ __global__ void __launch_bounds__(NT, 2) list_metrics_warp_kernel(const LmParams
             if (lane == owner) {
 #pragma unroll
                 for (int j = 0; j < KT; ++j) s_row[j] = ids[j];
-                for (int j = 0; j < Kb; ++j)                               // un-set what the pass above set
-                    *reinterpret_cast<uint32_t *>(bits_base + (s_row[j] & ~31u) * 4u) = 0u;
-                uint64_t seen = 0;
-                n_b = 0; inter = 0; serp = 0; prag = 0;
-                for (int j = 0; j < Kb; ++j) {
-                    const unsigned id = s_row[j];
-                    if (id >= vocab) { ++oov; continue; }
-                    uint32_t *wp = reinterpret_cast<uint32_t *>(bits_base + (id & ~31u) * 4u);
-                    const uint32_t w = *wp, bit = 1u << (id & 31u);
-                    if (w & bit) continue;
-                    *wp = w | bit;
-                    ++n_b;
-                    const unsigned tt = tab[id];
-                    if (tt != ABSENT) {
-                        const unsigned r = 63u - tt;
-                        ++inter;
-                        if constexpr (RANK) {
-                            serp += Kn - j;
-                            prag += __popcll(seen & ((1ull << r) - 1ull));
-                        }
-                        seen |= 1ull << r;
-                    } else if constexpr (RANK) {
-                        prag += __popcll(seen);
-                    }
+            }
+            const int Ko = __shfl_sync(FULL, Kb, owner);
+            __syncwarp();
+            const unsigned id_a = s_row[lane < KT ? lane : 0];
+            const unsigned id_b = s_row[lane + 32 < KT ? lane + 32 : 0];
+            const bool in_a = lane < Ko, in_b = KT > 32 && lane + 32 < Ko;
+            bool dup_a = false, dup_b = false;
+            for (int k = 0; k < 32; ++k) {           // every lane sees every id of the row
+                const unsigned xa = __shfl_sync(FULL, id_a, k);
+                dup_a |= k < lane && xa == id_a;
+                if constexpr (KT > 32) {
+                    const unsigned xb = __shfl_sync(FULL, id_b, k);
+                    dup_b |= xa == id_b || (k < lane && xb == id_b);      // position k + 32 < Ko whenever lane + 32 is
                 }
+            }
+            const bool first_a = in_a && id_a < vocab && !dup_a;
+            const bool first_b = in_b && id_b < vocab && !dup_b;
+            const int foreign_n = __popc(__ballot_sync(FULL, in_a && id_a >= vocab)) +
+                                  __popc(__ballot_sync(FULL, in_b && id_b >= vocab));
+            const unsigned t_a = first_a ? tab[id_a] : ABSENT, t_b = first_b ? tab[id_b] : ABSENT;
+            const bool hit_a = t_a != ABSENT, hit_b = t_b != ABSENT;
+            const uint64_t m_a = hit_a ? 1ull << (63u - t_a) : 0ull;        // one-hot neutral ranks
+            const uint64_t m_b = hit_b ? 1ull << (63u - t_b) : 0ull;
+            uint64_t inc_a = m_a, inc_b = m_b;                               // inclusive prefix-ORs over lanes
+#pragma unroll
+            for (int off = 1; off < 32; off <<= 1) {
+                const uint64_t ya = __shfl_up_sync(FULL, inc_a, off), yb = __shfl_up_sync(FULL, inc_b, off);
+                if (lane >= off) { inc_a |= ya; inc_b |= yb; }
+            }
+            uint64_t before_a = __shfl_up_sync(FULL, inc_a, 1), before_b = __shfl_up_sync(FULL, inc_b, 1);
+            if (lane == 0) { before_a = 0; before_b = 0; }
+            before_b |= __shfl_sync(FULL, inc_a, 31);
+            const int c_nb = __popc(__ballot_sync(FULL, first_a)) + __popc(__ballot_sync(FULL, first_b));
+            const int c_in = __popc(__ballot_sync(FULL, hit_a)) + __popc(__ballot_sync(FULL, hit_b));
+            int c_serp = (hit_a ? Kn - lane : 0) + (hit_b ? Kn - lane - 32 : 0);
+            int c_prag = (first_a ? __popcll(hit_a ? before_a & (m_a - 1ull) : before_a) : 0) +
+                         (first_b ? __popcll(hit_b ? before_b & (m_b - 1ull) : before_b) : 0);
+#pragma unroll
+            for (int off = 16; off >= 1; off >>= 1) {
+                c_serp += __shfl_xor_sync(FULL, c_serp, off);
+                c_prag += __shfl_xor_sync(FULL, c_prag, off);
+            }
+            if (lane == owner) {
+                n_b = c_nb; inter = c_in; serp = c_serp; prag = c_prag;
+                oov += foreign_n;
             }
             __syncwarp();
         }
