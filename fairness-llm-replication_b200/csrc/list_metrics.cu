@@ -560,6 +560,17 @@ __device__ __forceinline__ uint64_t shr64_clamped(uint64_t v, unsigned amount) {
     return r;
 }
 
+__device__ __forceinline__ uint32_t shl32_clamped(uint32_t v, unsigned amount) {   // amount may be >= 32 (-> 0)
+    uint32_t r;
+    asm("shl.b32 %0, %1, %2;" : "=r"(r) : "r"(v), "r"(amount));
+    return r;
+}
+__device__ __forceinline__ uint32_t shr32_clamped(uint32_t v, unsigned amount) {
+    uint32_t r;
+    asm("shr.b32 %0, %1, %2;" : "=r"(r) : "r"(v), "r"(amount));
+    return r;
+}
+
 constexpr int WK_WARPS = NT / 32;
 
 struct WkSmem {
@@ -584,7 +595,11 @@ template <int KT, bool RANK>
 __global__ void __launch_bounds__(NT, 2) list_metrics_warp_kernel(const LmParams p) {
     extern __shared__ __align__(128) unsigned char smem[];
     constexpr unsigned FULL = 0xffffffffu;
-    constexpr unsigned ABSENT = 64u;                     // table entry of an id that is not in the neutral list
+    // Table entry of a neutral item of rank r: TOP - r; of an id that is not in the neutral list: TOP + 1.
+    // Rows of at most 32 items keep their rank masks in one 32-bit word.
+    constexpr bool NARROW = KT <= 32;
+    constexpr unsigned TOP = NARROW ? 31u : 63u, ABSENT = TOP + 1u, ABSENT_SHIFT = NARROW ? 5u : 6u;
+    constexpr int ABSENT4 = static_cast<int>(ABSENT * 0x01010101u);
     static_assert(KT % 2 == 0 && KT <= 62, "row length must be even; t = 63 - rank must stay >= 1");
     const int K = p.K, V = p.V, Kn = p.k_cap;
     const unsigned vocab = static_cast<unsigned>(p.vocab);
@@ -608,7 +623,7 @@ __global__ void __launch_bounds__(NT, 2) list_metrics_warp_kernel(const LmParams
 
     for (int i = t; i <= 2 * KT; i += NT) s_recip[i] = i > 0 ? 1.0 / static_cast<double>(i) : 0.0;
     for (int i = lane; i < tab_bytes16; i += 32)
-        reinterpret_cast<int4 *>(tab)[i] = make_int4(0x40404040, 0x40404040, 0x40404040, 0x40404040);
+        reinterpret_cast<int4 *>(tab)[i] = make_int4(ABSENT4, ABSENT4, ABSENT4, ABSENT4);
     for (int w = 0; w < own_row + 3; ++w) s_bits[w * 32 + lane] = w == own_row ? foreign_bit : 0u;
     if (lane == 0) {
         mbar_init(bar, 1);
@@ -705,7 +720,7 @@ __global__ void __launch_bounds__(NT, 2) list_metrics_warp_kernel(const LmParams
             const int Ka = max(0, min(nlen, Kn));
             const unsigned id0 = lane < Ka ? nid0 : vocab, id1 = lane + 32 < Ka ? nid1 : vocab;
             oov += (lane < Ka && id0 >= vocab ? 1 : 0) + (lane + 32 < Ka && id1 >= vocab ? 1 : 0);
-            const unsigned t0 = 63u - lane, t1 = 31u - lane;            // t of positions lane and lane + 32
+            const unsigned t0 = TOP - lane, t1 = TOP - 32u - lane;      // t of positions lane and lane + 32 (t1 unused when NARROW)
             if (id1 < vocab) tab[id1] = static_cast<uint8_t>(t1);       // later half first,
             __syncwarp();
             if (id0 < vocab) tab[id0] = static_cast<uint8_t>(t0);       // so the earlier half wins
@@ -726,7 +741,7 @@ __global__ void __launch_bounds__(NT, 2) list_metrics_warp_kernel(const LmParams
 
         // ---- optimistic pass over the row ----
         char *bits_base = reinterpret_cast<char *>(s_bits + lane);
-        uint32_t seen_lo = 0, seen_hi = 0;      // bit 63 - r = neutral rank r was hit
+        uint32_t seen_lo = 0, seen_hi = 0;      // bit TOP - r = neutral rank r was hit
         uint32_t repeat = 0, absent_pos = 0;
         int below = 0;
 #pragma unroll
@@ -736,15 +751,20 @@ __global__ void __launch_bounds__(NT, 2) list_metrics_warp_kernel(const LmParams
             const uint32_t bit = 1u << (idx & 31u);
             const uint32_t old = atomicOr(wp, bit);
             repeat |= old & bit;
-            const unsigned tt = tab[idx];                  // 63 - rank, 64 when absent
-            if constexpr (RANK) {
-                const uint64_t seen = (static_cast<uint64_t>(seen_hi) << 32) | seen_lo;
-                below += __popcll(shr64_clamped(seen, tt));         // hits so far ranked before this one (absent: 0)
-                absent_pos += (tt >> 6) * static_cast<unsigned>(j);
+            const unsigned tt = tab[idx];                  // TOP - rank, TOP + 1 when absent
+            if constexpr (RANK) absent_pos += (tt >> ABSENT_SHIFT) * static_cast<unsigned>(j);
+            if constexpr (NARROW) {
+                if constexpr (RANK) below += __popc(shr32_clamped(seen_lo, tt));    // hits so far ranked before this one (absent: 0)
+                seen_lo += shl32_clamped(1u, tt);                                    // absent: 0; bits of a clean row are distinct: + is |
+            } else {
+                if constexpr (RANK) {
+                    const uint64_t seen = (static_cast<uint64_t>(seen_hi) << 32) | seen_lo;
+                    below += __popcll(shr64_clamped(seen, tt));
+                }
+                const uint64_t own = shl64_clamped(1ull, tt);
+                seen_lo += static_cast<uint32_t>(own);
+                seen_hi += static_cast<uint32_t>(own >> 32);
             }
-            const uint64_t own = shl64_clamped(1ull, tt);           // absent: 0
-            seen_lo += static_cast<uint32_t>(own);                  // bits of a clean row are distinct: + is |
-            seen_hi += static_cast<uint32_t>(own >> 32);
         }
         // A clean row of Kb elements with hits at positions p_1 < ... < p_h: a miss counts the hits before
         // it, which adds up to h (Kb - 1) - sum p_i - h (h - 1) / 2; spares past the end count nothing.
@@ -786,8 +806,8 @@ __global__ void __launch_bounds__(NT, 2) list_metrics_warp_kernel(const LmParams
                                   __popc(__ballot_sync(FULL, in_b && id_b >= vocab));
             const unsigned t_a = first_a ? tab[id_a] : ABSENT, t_b = first_b ? tab[id_b] : ABSENT;
             const bool hit_a = t_a != ABSENT, hit_b = t_b != ABSENT;
-            const uint64_t m_a = hit_a ? 1ull << (63u - t_a) : 0ull;        // one-hot neutral ranks
-            const uint64_t m_b = hit_b ? 1ull << (63u - t_b) : 0ull;
+            const uint64_t m_a = hit_a ? 1ull << (TOP - t_a) : 0ull;        // one-hot neutral ranks
+            const uint64_t m_b = hit_b ? 1ull << (TOP - t_b) : 0ull;
             uint64_t inc_a = m_a, inc_b = m_b;                               // inclusive prefix-ORs over lanes
 #pragma unroll
             for (int off = 1; off < 32; off <<= 1) {
