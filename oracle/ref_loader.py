@@ -1,6 +1,7 @@
 """Import the UNMODIFIED reference modules from /root/reference/src.
-TEST INFRASTRUCTURE ONLY; works only in the build container (the GPU box has no
-/root/reference), so nothing under ``-m gpu``, ``smoke()`` or ``bench.py`` may call it.
+TEST INFRASTRUCTURE ONLY.  /root/reference exists only in the build container, so nothing under
+``-m gpu`` or ``smoke()`` calls this; the one use on the GPU box is the timed reference arm of
+``bench.py``, which loads the copy that ``oracle/build_ref.py`` staged in ``oracle/_ref`` (STAGED_SRC).
 
 ``src/config.py`` is git-ignored upstream (SURVEY.md Fact 3), so a stub module with
 the attributes the phase scripts read at import time is injected first.
@@ -16,10 +17,11 @@ import sys
 import types
 
 REF_SRC = "/root/reference/src"
+STAGED_SRC = os.path.join(os.path.dirname(os.path.abspath(__file__)), "_ref")   # oracle/build_ref.py
 
 
-def available() -> bool:
-    return os.path.isfile(os.path.join(REF_SRC, "utils.py"))
+def available(src: str = REF_SRC) -> bool:
+    return os.path.isfile(os.path.join(src, "utils.py"))
 
 
 def _stub_config() -> types.ModuleType:
@@ -40,16 +42,17 @@ def _stub_config() -> types.ModuleType:
     return cfg
 
 
-def load(name: str):
+def load(name: str, src: str = REF_SRC):
     """Return reference module ``utils`` / ``phase1_bias_detection`` /
-    ``phase3_facter_mitigation`` under the private name ``_flr_ref_<name>``."""
-    if not available():
-        raise RuntimeError("reference tree not present (expected only in the build container)")
+    ``phase3_facter_mitigation`` under the private name ``_flr_ref_<name>``, from the reference
+    tree (build container) or from ``STAGED_SRC``."""
+    if not available(src):
+        raise RuntimeError("reference modules not found under %s" % src)
     sys.dont_write_bytecode = True
     saved_path = list(sys.path)
     saved = {k: sys.modules.get(k) for k in ("config", "utils")}
     try:
-        sys.path.insert(0, REF_SRC)
+        sys.path.insert(0, src)
         sys.modules["config"] = _stub_config()
         sys.modules.pop("utils", None)
         mod = importlib.import_module(name)
