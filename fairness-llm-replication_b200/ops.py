@@ -15,10 +15,10 @@ import torch
 
 from . import _lib
 from ._lib import (DTYPE_F32, DTYPE_F64, EMPTY_ANY_IS_ZERO, EMPTY_BOTH_IS_ONE,  # noqa: F401 (re-exported)
-                   SELECT_BINS, SELECT_STATE_WORDS)
+                   MAX_RANK_K, SELECT_BINS, SELECT_STATE_WORDS)
 
 __all__ = [
-    "list_metrics", "ListMetrics", "pair_jaccard", "cosine_nonconformity", "radix_select",
+    "list_metrics", "ListMetrics", "list_metrics_kernel_name", "cosine_kernel_name", "pair_jaccard", "cosine_nonconformity", "radix_select",
     "threshold_schedule", "violation_detect", "conformal_keep_len", "normalize_rows_bf16",
     "pair_similarity", "group_item_histogram", "js_distance_matrix", "equal_opportunity_counts", "ndcg", "exposure_by_group", "synth_lists", "synth_embeddings", "synth_lists_host",
     "synth_embeddings_host", "zipf_cdf_host", "device_info",
@@ -117,6 +117,29 @@ def list_metrics(neutral, neutral_len, lists, lens, *, vocab: int, k_cap: Option
               _ptr(inter), _ptr(union), _ptr(jac), _ptr(serp), _ptr(prag), _ptr(sums), _ptr(status),
               _ptr(ws), ws.numel(), _stream())
     return ListMetrics(inter, union, jac, serp, prag, sums, status, min(k_cap, K))
+
+
+def list_metrics_kernel_name(V: int, K: int, vocab: int, k_cap: Optional[int] = None, rank_metrics: bool = True) -> str:
+    """Name of the kernel ``list_metrics`` launches for a shape (the plan of csrc/list_metrics.cu:make_plan),
+    for labelling measurements: what ncu and the profiler list is this name."""
+    k_cap = K if k_cap is None else min(k_cap, K)
+    r = 1 if rank_metrics else 0
+    if 0 < vocab <= 16384 and k_cap <= MAX_RANK_K and 2 <= V <= 128:
+        cap = next((c for c in (10, 20, 32, 50, 62) if K <= c), 0)
+        if cap and 17 <= V <= 32:
+            return "list_metrics_warp_kernel<%d,%d>" % (cap, r)
+        if cap:
+            return "list_metrics_reg_kernel<%d,%d>" % (cap, r)
+        return "list_metrics_table_kernel<%d,%d>" % (4 if K % 4 == 0 else 2 if K % 2 == 0 else 1, r)
+    return "list_metrics_cmp_kernel<%d>" % r
+
+
+def cosine_kernel_name(V: int, D: int) -> str:
+    """Name of the kernel ``cosine_nonconformity`` launches (csrc/cosine.cu:launch_cos)."""
+    nc = (D + 127) // 128
+    if (V + 1) * D * 4 * 2 <= 200 * 1024:
+        return "cosine_tma_kernel<%d,%d>" % (nc, 1 if D == nc * 128 else 0)
+    return "cosine_kernel<%d>" % nc
 
 
 def pair_jaccard(lists, lens, *, vocab: int):

@@ -123,6 +123,12 @@ class ScoringPipeline:
         self.kernel_events.append((name, a, b))
         return out
 
+    def kernel_names(self) -> Tuple[str, str]:
+        """The two kernels that carry a step's bytes, by the names the profiler shows."""
+        cfg = self.cfg
+        return (ops.list_metrics_kernel_name(cfg.n_variants, cfg.list_len, cfg.vocab, cfg.k_cap),
+                ops.cosine_kernel_name(cfg.n_variants, cfg.emb_dim))
+
     # -- collectives -------------------------------------------------------------------
     def _all_reduce(self, t: torch.Tensor) -> None:
         if self.distributed:
@@ -135,10 +141,10 @@ class ScoringPipeline:
         V, R = cfg.n_variants, cfg.rounds
         dev = b.lists.device
         hist0 = torch.zeros(ops.SELECT_BINS, dtype=torch.int64, device=dev)
-        lm = self._timed("list_metrics_table_kernel", lambda: ops.list_metrics(
+        lm = self._timed(self.kernel_names()[0], lambda: ops.list_metrics(
             b.neutral, b.neutral_len, b.lists, b.lens, vocab=cfg.vocab, k_cap=cfg.k_cap,
             empty_policy=cfg.empty_policy, rank_metrics=True, want_union=False, want_sums=True))
-        scores = self._timed("cosine_kernel", lambda: ops.cosine_nonconformity(b.emb_neutral, b.emb, hist0=hist0))
+        scores = self._timed(self.kernel_names()[1], lambda: ops.cosine_nonconformity(b.emb_neutral, b.emb, hist0=hist0))
         self.n_launches += 3
         return self._finish(lm.inter, lm.jaccard, lm.serp, lm.prag, lm.variant_sums, lm.status, scores, hist0)
 
@@ -255,3 +261,37 @@ class ScoringPipeline:
                 "variant_violation_counts": vcounts, "n_scores": int(st[ops._lib.ST_N]),
                 "select_rank": int(st[ops._lib.ST_K]), "n_users": int(sums[0, 3]),
                 "oov_ids": int(res.status.item())}
+
+
+def multi_gpu_parity(cfg: PipelineConfig, rank: int, world: int, device, users_per_rank: int = 8192,
+                     process_group=None) -> Optional[dict]:
+    """Correctness witness of the sharded path on real hardware.
+
+    Every rank scores its own shard of ``users_per_rank`` users with the collectives on; rank 0 then
+    scores the union of all shards alone on its GPU.  The global quantities must agree exactly --
+    thresholds, select state (n, k, less, equal), violation counts, the integer SERP*/PRAG* sums --
+    the Jaccard sums to 1e-12, and rank 0's per-pair outputs must equal the first slice of the union run.
+    Returns the verdict on rank 0, None elsewhere.  Collective: every rank must call it."""
+    V = cfg.n_variants
+    shard = synth_batch(cfg, rank * users_per_rank, users_per_rank, device)
+    res = ScoringPipeline(cfg, distributed=world > 1, process_group=process_group).run(shard)
+    torch.cuda.synchronize(device)
+    if rank != 0:
+        return None
+    union = synth_batch(cfg, 0, world * users_per_rank, device)
+    one = ScoringPipeline(cfg).run(union)
+    torch.cuda.synchronize(device)
+    red_n, red_1 = res.reduced.cpu().numpy(), one.reduced.cpu().numpy()
+    sums_n, sums_1 = red_n[:V * 4].reshape(V, 4), red_1[:V * 4].reshape(V, 4)
+    n = users_per_rank
+    checks = {
+        "thresholds": bool(torch.equal(res.thresholds, one.thresholds)),
+        "select_state": bool(torch.equal(res.select_state, one.select_state)),
+        "violation_counts": bool(np.array_equal(red_n[V * 4:], red_1[V * 4:])),
+        "integer_sums": bool(np.array_equal(sums_n[:, 1:], sums_1[:, 1:])),
+        "jaccard_sums_1e-12": bool(np.allclose(sums_n[:, 0], sums_1[:, 0], rtol=1e-12, atol=0)),
+        "shard0_pairs": bool(torch.equal(res.inter, one.inter[:n]) and torch.equal(res.scores, one.scores[:n])
+                             and torch.equal(res.flags, one.flags[:n]) and torch.equal(res.prag, one.prag[:n])),
+    }
+    return {"multi_gpu_parity": all(checks.values()), "ranks": world, "users_per_rank": users_per_rank,
+            "checks": checks}
