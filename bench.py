@@ -357,7 +357,37 @@ def other_configs(dev, peak):
         "gemm_tflops": U * 2.0 * M * M * D / (ms_gemm * 1e-3) / 1e12,
         "normalize_ms": ms_norm, "pair_jaccard_ms": ms_pj,
         "pair_jaccard_list_pairs_per_s": U * M * (M - 1) / 2 / (ms_pj * 1e-3),
+        "normalize_gbs": U * M * D * 6 / (ms_norm * 1e-3) / 1e9,
+        "normalize_frac_of_measured_hbm": U * M * D * 6 / (ms_norm * 1e-3) / 1e9 / peak,
+        "pair_jaccard_gbs": U * (M * K * 4 + M * 4 + M * M * 4 + M * 4) / (ms_pj * 1e-3) / 1e9,
+        "pair_jaccard_frac_of_measured_hbm": U * (M * K * 4 + M * 4 + M * M * 4 + M * 4) / (ms_pj * 1e-3) / 1e9 / peak,
         "note": "GEMM is HBM-bound (75 flop/B): tensor-pipe utilisation is low by construction"}
+    del l4, n4, e4, xh
+    # a9 with the reference's per-group semantics (src/phase3_facter_mitigation.py:159-178): 1M scores in 31 groups
+    N = 1_000_000
+    g = torch.Generator(device=dev); g.manual_seed(1)
+    sc32 = torch.rand(N, device=dev, generator=g)
+    grp = torch.randint(0, 31, (N,), device=dev, generator=g, dtype=torch.int32).to(torch.uint8)
+    sc64 = sc32.double()
+    ms32 = timed(lambda: ops.radix_select(sc32, alpha=0.1, groups=grp, n_groups=31), flush=flush)
+    ms64 = timed(lambda: ops.radix_select(sc64, alpha=0.1, groups=grp, n_groups=31), flush=flush)
+    out["a9_select_per_group_1M_x_31_groups"] = {
+        "f32_ms": ms32, "f32_gbs": 3 * N * 5 / (ms32 * 1e-3) / 1e9, "f32_frac_of_measured_hbm": 3 * N * 5 / (ms32 * 1e-3) / 1e9 / peak,
+        "f64_ms": ms64, "f64_gbs": 6 * N * 9 / (ms64 * 1e-3) / 1e9, "f64_frac_of_measured_hbm": 6 * N * 9 / (ms64 * 1e-3) / 1e9 / peak,
+        "note": "whole select (3 passes f32 / 6 passes f64: histogram + scan each, torch allocations included); "
+                "5 MB of scores + group ids: latency-bound, the fraction of HBM is for the record"}
+    del sc32, sc64, grp
+    # N1: demographic-parity item histogram over the bench shard's lists (dense [U, V, K] layout)
+    Uh = 1_250_000
+    _, _, lh, nh = ops.synth_lists(pipeline.SEED, 0, Uh, 31, 50, 3706, dev)
+    ms_h = timed(lambda: ops.group_item_histogram(lh, nh, vocab=3706, n_groups=31), reps=5)
+    hb_bytes = Uh * 31 * (50 * 4 + 4)
+    out["n1_group_item_histogram_1250k_users"] = {
+        "rows": Uh * 31, "ms": ms_h, "gbs": hb_bytes / (ms_h * 1e-3) / 1e9,
+        "frac_of_measured_hbm": hb_bytes / (ms_h * 1e-3) / 1e9 / peak, "kernel": "dense_group_histogram_kernel"}
+    hist = ops.group_item_histogram(lh, nh, vocab=3706, n_groups=31)
+    out["n1_js_distance_matrix_31_groups_ms"] = timed(lambda: ops.js_distance_matrix(hist))
+    del lh, nh
     return out
 
 # ---------------------------------------------------------------------------------- our arm
@@ -445,7 +475,35 @@ def run_ours(args):
                "h2d_gbs_per_gpu": hb.nbytes() * e2e_steps / dt / 1e9,      # PCIe is the bound here (~55 GB/s on Gen5 x16)
                "note": "ScoringPipeline.run_host: chunked H2D from pinned memory overlapped with the kernels",
                "cpu_binding_rank0": numa}
+        # ---- what the host->device path of this box can do with no kernel at all: the same pinned batch,
+        #      the same chunks, copies only; all ranks at once (they share the host's memory and PCIe roots)
+        bufs = pipe._staging(dev, 16384)
+        copy = pipe._copy_stream(dev)
+        def copies_only():
+            with torch.cuda.stream(copy):
+                for c in range((E + 16383) // 16384):
+                    lo, hi = c * 16384, min(E, (c + 1) * 16384)
+                    for dst, src in zip(bufs[c & 1], hb.tensors()):
+                        dst[:hi - lo].copy_(src[lo:hi], non_blocking=True)
+            copy.synchronize()
+        copies_only()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(e2e_steps):
+            copies_only()
+        barrier()
+        dt_copy = max_over_ranks(time.perf_counter() - t0)
+        e2e["h2d_ceiling_gbs_per_gpu"] = hb.nbytes() * e2e_steps / dt_copy / 1e9
+        e2e["h2d_frac_of_ceiling"] = e2e["h2d_gbs_per_gpu"] / e2e["h2d_ceiling_gbs_per_gpu"]
+        e2e["ceiling_note"] = ("copies only, no kernels, all %d ranks at once: what is left between this and the "
+                               "e2e rate is software, what is below the link rate is the host" % n_gpus)
         del hb
+
+    # ---- multi-GPU correctness witness (outside every timed region): sharded run vs the union on rank 0
+    parity = None
+    if distributed:
+        parity = pipeline.multi_gpu_parity(cfg, rank, world, dev, users_per_rank=args.parity_users)
+        barrier()
 
     extra = None
     if rank == 0 and n_gpus == 1 and not args.no_other_configs:
@@ -455,16 +513,29 @@ def run_ours(args):
     if rank == 0:
         peak, peak_src = hbm_peak()
         pairs_gpu = U * V
-        roof = {}
-        for name, bytes_per_pair in (("cosine_kernel", D * 4 * (V + 1) / V + 4),
-                                     ("list_metrics_table_kernel", K * 4 * (V + 1) / V + 4 * (V + 1) / V + 16)):
+        lm_name, cos_name = pipe.kernel_names()
+        records = []
+        for name, bytes_per_pair in ((cos_name, D * 4 * (V + 1) / V + 4),
+                                     (lm_name, K * 4 * (V + 1) / V + 4 * (V + 1) / V + 16)):
             if kernel_ms.get(name):
                 t = float(np.mean(kernel_ms[name])) * 1e-3
                 ach = pairs_gpu * bytes_per_pair / t / 1e9
-                roof[name] = {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
-                              "traffic": ncu_traffic(name, pairs_gpu), "kernel": name, "avg_launch_ms": t * 1e3,
-                              "algorithmic_bytes_per_launch": pairs_gpu * bytes_per_pair,
-                              "peak_source": peak_src, "frac_of_nominal_8000": ach / 8000.0}
+                records.append({"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
+                                "traffic": ncu_traffic(name, pairs_gpu), "kernel": name, "avg_launch_ms": t * 1e3,
+                                "algorithmic_bytes_per_launch": pairs_gpu * bytes_per_pair,
+                                "share_of_step_kernel_time": None,
+                                "peak_source": peak_src, "frac_of_nominal_8000": ach / 8000.0})
+        t_all = sum(r["avg_launch_ms"] for r in records) or 1.0
+        for r in records:
+            r["share_of_step_kernel_time"] = r["avg_launch_ms"] / t_all
+        # `roofline` is the dominant kernel's record (most of the step's time and bytes); the records of every
+        # step kernel, weakest included, ride inside it so that they stay with the line
+        roofline = None
+        if records:
+            roofline = dict(max(records, key=lambda r: r["avg_launch_ms"]))
+            roofline["step_kernels"] = records
+            roofline["worst_frac"] = min(r["frac"] for r in records)
+            roofline["worst_kernel"] = min(records, key=lambda r: r["frac"])["kernel"]
         cpu = None
         if n_gpus == 1 and not args.no_cpu_baseline:
             # bounded sample: batches of --cpu-sample-users users until about 10 s of scoring time
@@ -476,18 +547,26 @@ def run_ours(args):
             cpu = {"value": reps * n * V / t_sum, "unit": UNIT, "cores": cores, "kind": "port",
                    "sample": "%d batches of %d users x %d variants, full pipeline, %.1f s of scoring on %d cores"
                              % (reps, n, V, t_sum, cores)}
-            cpu["string_api_single_thread"] = string_api_sample(args)
+            mods = reference_modules()
+            if mods is not None:       # the reference's own functions on one thread, beside the port
+                v_ref, dt_ref, parts = reference_sample(args, mods, args.ref_sample_users)
+                cpu["reference_single_thread"] = {
+                    "value": v_ref, "unit": UNIT, "cores": 1, "kind": "reference",
+                    "sample": "%d users x %d variants: calculate_individual_fairness %.2f s + "
+                              "calculate_conformal_thresholds %.2f s (no SERP*/PRAG*/cosine in the reference)"
+                              % (args.ref_sample_users, V, parts["jaccard_s"], parts["threshold_s"])}
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": n_gpus, "steps": steps, "warmup": warm,
             "ms_per_step": ms_total / steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic", "config": workload_config(args, n_gpus), "e2e": e2e,
             "gpu_launches": launches, "clocks": clocks,
-            "roofline": roof.get("cosine_kernel"), "roofline_list_metrics": roof.get("list_metrics_table_kernel"),
+            "roofline": roofline,
             "cpu_baseline": cpu,
             "step_kernel_ms": {k: float(np.mean(v)) for k, v in kernel_ms.items()},
             "other_configs": extra,
-            "check": {"threshold": float(summary["thresholds"][0]), "violations_round0": int(summary["violation_counts"][0]),
-                      "mean_jaccard_v0": float(summary["variant_means"][0, 0])},
+            "check": dict({"threshold": float(summary["thresholds"][0]),
+                           "violations_round0": int(summary["violation_counts"][0]),
+                           "mean_jaccard_v0": float(summary["variant_means"][0, 0])}, **(parity or {})),
         }
         print(json.dumps(line))
     if distributed:

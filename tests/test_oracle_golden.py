@@ -1,5 +1,8 @@
 """The CPU oracle against the golden vectors produced by the unmodified reference
 (oracle/make_golden.py -> tests/golden/reference_golden.json).  No GPU."""
+import json
+import os
+
 import numpy as np
 import pandas as pd
 import pytest
@@ -262,3 +265,43 @@ def test_ranking_metrics_port(golden):
         assert [[a, float(b)] for a, b in nd.items()] == c["ndcg_per_group"]
         gt = {it["id"]: it.get("relevance_score", 0.5) for it in c["items"]}
         assert float(R.calculate_ndcg(c["ranked"], gt, c["k"])) == c["ndcg_all"]
+
+
+def test_cpu_input_generator_matches_the_products_host_generator(lib):
+    """oracle/synth_ref.c (plain C, used by the CPU arms of bench.py) restates the product's generator:
+    identical bytes for lists, lengths and embeddings, at the benchmark shape and at an odd one."""
+    from fairness_llm_replication_b200 import ops
+    from oracle import synth_ref
+    for seed, user0, U, V, K, vocab in ((20251203, 12345, 257, 31, 50, 3706), (7, 0, 64, 5, 13, 90)):
+        mine = synth_ref.lists(seed, user0, U, V, K, vocab)
+        theirs = ops.synth_lists_host(seed, user0, U, V, K, vocab)
+        for a, b in zip(mine, theirs):
+            assert a.dtype == b.dtype and np.array_equal(a, b)
+    for a, b in zip(synth_ref.embeddings(20251203, 99, 33, 31, 384), ops.synth_embeddings_host(20251203, 99, 33, 31, 384)):
+        assert a.dtype == b.dtype and np.array_equal(a, b)
+
+
+def test_reference_arm_runs_without_the_cuda_library():
+    """`bench.py --impl reference` must not map libflr_b200.so: run it in a fresh process and
+    read its own /proc/self/maps from inside."""
+    import subprocess, sys, textwrap
+    code = textwrap.dedent("""
+        import sys, json, io, contextlib
+        sys.argv = ["bench.py", "--impl", "reference", "--steps", "1", "--warmup", "0",
+                    "--ref-sample-users", "64", "--cpu-sample-users", "64"]
+        import bench
+        buf = io.StringIO()
+        with contextlib.redirect_stdout(buf):
+            bench.run_reference(bench.parse_args())
+        line = json.loads(buf.getvalue())
+        maps = open("/proc/self/maps").read()
+        print(json.dumps({"kind": line["cpu_baseline"]["kind"], "impl": line["impl"], "value": line["value"],
+                          "maps_flr": "libflr_b200" in maps, "torch": "torch" in sys.modules}))
+    """)
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, "-c", code], cwd=root, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr[-2000:]
+    out = json.loads(r.stdout.strip().splitlines()[-1])
+    assert out["impl"] == "reference" and out["value"] > 0
+    assert out["kind"] in ("reference", "port")
+    assert not out["maps_flr"] and not out["torch"]
