@@ -11,7 +11,14 @@ KEYS = ["Kernel Name", "launch__grid_size", "launch__block_size", "launch__regis
         "smsp__issue_active.avg.pct_of_peak_sustained_active", "smsp__inst_executed.sum",
         "sm__inst_executed_pipe_lsu.avg.pct_of_peak_sustained_active",
         "sm__inst_executed_pipe_fp64.avg.pct_of_peak_sustained_active",
-        "l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum", "lts__throughput.avg.pct_of_peak_sustained_elapsed"]
+        "l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum", "lts__throughput.avg.pct_of_peak_sustained_elapsed",
+        "sm__inst_executed_pipe_alu.avg.pct_of_peak_sustained_active", "sm__inst_executed_pipe_fma.avg.pct_of_peak_sustained_active",
+        "sm__inst_executed_pipe_xu.avg.pct_of_peak_sustained_active", "l1tex__data_pipe_lsu_wavefronts.avg.pct_of_peak_sustained_elapsed",
+        "sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active",
+        "sm__inst_executed_pipe_tensor_subpipe_hmma.avg.pct_of_peak_sustained_active",
+        "sm__ops_path_tensor_op_hmma_src_bf16_dst_fp32_sparsity_off.avg.pct_of_peak_sustained_elapsed",
+        "smsp__sass_average_data_bytes_per_sector_mem_global_op_st.ratio",
+        "smsp__sass_average_data_bytes_per_sector_mem_global_op_ld.ratio"]
 
 def main():
     rep, out = sys.argv[1], sys.argv[2]
@@ -31,15 +38,15 @@ def main():
     traffic = {}
     for r in data:
         name = r[idx["Kernel Name"]]
-        short = ("cosine_kernel" if "cosine" in name else
-                 "list_metrics_table_kernel" if ("list_metrics_table" in name or "list_metrics_reg" in name) else name)
+        # family name as bench.py labels it: unqualified, no template arguments
+        short = name.replace("void ", "").replace("<unnamed>::", "").split("(")[0].split("<")[0].strip()
         b = (to_bytes(r[idx["dram__bytes_read.sum"]], units[idx["dram__bytes_read.sum"]]) +
              to_bytes(r[idx["dram__bytes_write.sum"]], units[idx["dram__bytes_write.sum"]]))
         traffic.setdefault(short, []).append(b)
     tj = os.path.join(os.path.dirname(os.path.abspath(__file__)), "traffic.json")
     pairs = float(sys.argv[3]) if len(sys.argv) > 3 else None      # (user, variant) pairs per captured launch
     note = sys.argv[4] if len(sys.argv) > 4 else ""
-    per_launch = {k: sum(v) / len(v) for k, v in traffic.items()}
+    per_launch = {k: v[0] for k, v in traffic.items()}        # the first captured launch of each family
     json.dump({"source": os.path.basename(out), "note": note, "pairs_per_captured_launch": pairs,
                "dram_bytes_per_launch": per_launch,
                "dram_bytes_per_pair": {k: v / pairs for k, v in per_launch.items()} if pairs else None},
