@@ -8,7 +8,8 @@
 //   * one thread issues tcgen05.mma (kind::f16, bf16 x bf16 -> fp32, M = N = 128, K = 16 per
 //     instruction) into a 128-column TMEM accumulator, double-buffered so the epilogue of user i
 //     overlaps the MMAs of user i+1;
-//   * four epilogue warps read their 32-lane TMEM quarter with tcgen05.ld and store the M x M block.
+//   * four epilogue warps read their 32-lane TMEM quarter with tcgen05.ld and store the M x M block
+//     through a small shared-memory stage, as full 128-byte row segments.
 // Warp roles: 0 = TMA producer, 1 = TMEM allocator + MMA issuer, 2..5 = epilogue.  Persistent
 // CTAs, one per SM; smem ring of 2 stages (96 KB each at D = 384).
 // The kernel moves 95 KB in and 61.5 KB out per user for 11.8 MFLOP: HBM-bound (75 flop/B).
@@ -108,6 +109,8 @@ constexpr int PS_TILE = 128;                 // UMMA M = N
 constexpr int PS_KBOX = 64;                  // bf16 columns per TMA box = one 128-byte swizzle row
 constexpr uint32_t PS_BOX_BYTES = PS_TILE * PS_KBOX * 2;     // 16 KB
 constexpr int PS_TMEM_COLS = 256;            // two 128-column fp32 accumulators
+constexpr int PS_STAGE_LD = 36;              // floats per row of an epilogue warp's [32][36] staging chunk
+constexpr size_t PS_EPI_BYTES = 4 * 32 * PS_STAGE_LD * sizeof(float);
 
 __device__ __forceinline__ void tma_load_2d(void *dst_smem, const CUtensorMap *tmap, int c0, int c1, uint64_t *bar) {
     asm volatile(
@@ -243,7 +246,12 @@ __global__ void __launch_bounds__(PS_THREADS, 1) pair_similarity_kernel(const __
         }
     } else {
         // ===== epilogue: warp w owns TMEM lanes [32 * (w % 4), +32) =====
+        // tcgen05.ld hands lane l row l of a 32 x 32 chunk.  Stored straight from there, one warp store
+        // would touch 32 different rows, 16 bytes each; so the chunk goes through a small shared-memory
+        // stage ([32][36] floats per warp: 128-bit accesses are conflict-free both ways) and leaves as
+        // full 128-byte row segments, four rows per store instruction.
         const int q = warp & 3;
+        float *stage = reinterpret_cast<float *>(tiles + static_cast<size_t>(p.stages) * p.stage_bytes) + q * (32 * PS_STAGE_LD);
         int a = 0;
         uint32_t aph = 0;
         const bool vec4 = (M % 4) == 0;
@@ -252,24 +260,32 @@ __global__ void __launch_bounds__(PS_THREADS, 1) pair_similarity_kernel(const __
             tcgen05_fence_after();
             const int row = q * 32 + lane;
             float *orow = p.out + (static_cast<size_t>(u) * M + row) * M;
+            float *oblock = p.out + (static_cast<size_t>(u) * M + q * 32) * M;
 #pragma unroll 1
             for (int c = 0; c < PS_TILE / 32; ++c) {
                 if (c * 32 >= M) break;
                 uint32_t r[32];
                 tmem_ld_32x32b_x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(a * PS_TILE + c * 32), r);
-                if (row < M) {
-                    if (vec4) {
+                if (vec4) {
+                    float4 *srow = reinterpret_cast<float4 *>(stage + lane * PS_STAGE_LD);
 #pragma unroll
-                        for (int j = 0; j < 32; j += 4)
-                            if (c * 32 + j < M)
-                                *reinterpret_cast<float4 *>(orow + c * 32 + j) =
-                                    make_float4(__uint_as_float(r[j]), __uint_as_float(r[j + 1]), __uint_as_float(r[j + 2]),
-                                                __uint_as_float(r[j + 3]));
-                    } else {
+                    for (int j = 0; j < 8; ++j)
+                        srow[j] = make_float4(__uint_as_float(r[4 * j]), __uint_as_float(r[4 * j + 1]),
+                                              __uint_as_float(r[4 * j + 2]), __uint_as_float(r[4 * j + 3]));
+                    __syncwarp();
+                    const int col = c * 32 + (lane & 7) * 4;
 #pragma unroll
-                        for (int j = 0; j < 32; ++j)
-                            if (c * 32 + j < M) orow[c * 32 + j] = __uint_as_float(r[j]);
+                    for (int i = 0; i < 8; ++i) {
+                        const int rl = i * 4 + (lane >> 3);
+                        if (q * 32 + rl < M && col < M)
+                            *reinterpret_cast<float4 *>(oblock + static_cast<size_t>(rl) * M + col) =
+                                *reinterpret_cast<const float4 *>(stage + rl * PS_STAGE_LD + (lane & 7) * 4);
                     }
+                    __syncwarp();
+                } else if (row < M) {
+#pragma unroll
+                    for (int j = 0; j < 32; ++j)
+                        if (c * 32 + j < M) orow[c * 32 + j] = __uint_as_float(r[j]);
                 }
             }
             tcgen05_fence_before();
@@ -362,8 +378,8 @@ extern "C" int flr_pair_similarity_gemm(const uint16_t *x_bf16, int64_t U, int M
     PsParams p{};
     p.U = U; p.M = M; p.D = D; p.kblocks = D / PS_KBOX; p.out = out;
     p.stage_bytes = static_cast<uint32_t>(p.kblocks) * PS_BOX_BYTES;
-    p.stages = std::max(1, std::min<int>(2, static_cast<int>((200u * 1024u) / p.stage_bytes)));
-    const size_t smem = static_cast<size_t>(p.stages) * p.stage_bytes + 1024;
+    p.stages = std::max(1, std::min<int>(2, static_cast<int>((200u * 1024u) / p.stage_bytes)));   // + 18 KB epilogue stage <= 227 KB
+    const size_t smem = static_cast<size_t>(p.stages) * p.stage_bytes + PS_EPI_BYTES + 1024;
     FLR_CUDA(cudaFuncSetAttribute(pair_similarity_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                   static_cast<int>(smem)));
     const int grid = static_cast<int>(std::min<int64_t>(U, device_sm_count()));
