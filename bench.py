@@ -308,6 +308,37 @@ def other_configs(dev, peak):
         "pairs": len(pairs), "ours_ms": 1e3 * float(np.median(ours)), "cpu_port_ms": 1e3 * float(np.median(port)),
         "identical": bool(r_ours[0] == r_port[0] and list(r_ours[1]) == list(r_port[1])),
         "note": "wall clock incl. string->id encoding, H2D, launch, D2H; at this size the host work is all there is"}
+    # the whole metric step of phase 1 (src/phase1_bias_detection.py:343-405) through the drop-in functions on a
+    # results-file-sized input: 1005 profiles (3 genders x 5 ages x 67), top-10 title lists; beside the same
+    # step composed from the string-level CPU port
+    from fairness_llm_replication_b200 import phase1_bias_detection as fast_p1
+    titles = ["Title %d (19%02d)" % (i, i % 100) for i in range(300)]
+    w = 1.0 / np.arange(1, 301)
+    big_profiles = [{"id": "q%d" % i, "gender": g, "age": a, "occupation": "professional"}
+                    for i, (g, a, _) in enumerate((g, a, r) for g in ("male", "female", "non-binary")
+                                                  for a in ("18-24", "25-34", "35-44", "45-54", "55+") for r in range(67))]
+    big_recs = {p_["id"]: {"profile_id": p_["id"], "recommendations":
+                           [titles[t] for t in rng.choice(300, size=10, replace=False, p=w / w.sum())]}
+                for p_ in big_profiles}
+    fast_p1.calculate_phase1_metrics(big_profiles[:30], big_recs)              # warm-up (module load, workspace)
+    t0 = time.perf_counter(); m_ours = fast_p1.calculate_phase1_metrics(big_profiles, big_recs); t_ours = time.perf_counter() - t0
+    t0 = time.perf_counter()
+    by_gender, by_age = {}, {}
+    for p_ in big_profiles:
+        by_gender.setdefault(p_["gender"], []).append(big_recs[p_["id"]]["recommendations"])
+        by_age.setdefault(p_["age"], []).append(big_recs[p_["id"]]["recommendations"])
+    dp_g = ref_port.calculate_demographic_parity(by_gender)[0]
+    dp_a = ref_port.calculate_demographic_parity(by_age)[0]
+    if_port = ref_port.measure_individual_fairness(big_profiles, big_recs)
+    eo_port = ref_port.calculate_equal_opportunity(by_gender, fast_p1.QUALIFIED_MOVIES)[0]
+    t_port = time.perf_counter() - t0
+    out["string_api_phase1_step_1005_profiles"] = {
+        "profiles": len(big_profiles), "pairs": int(m_ours["individual_fairness"]["details"]["num_pairs"]),
+        "ours_s": t_ours, "cpu_port_s": t_port, "speedup": t_port / t_ours,
+        "identical_individual_fairness": bool(float(m_ours["individual_fairness"]["score"]) == float(if_port[0])),
+        "demographic_parity_rel_diff": abs(float(m_ours["demographic_parity"]["gender"]["score"]) - float(dp_g)) / float(dp_g),
+        "note": "wall clock of calculate_phase1_metrics (pairs, 2 x demographic parity, individual fairness, equal "
+                "opportunity; lists encoded and uploaded once) vs the same step on the string-level CPU port"}
     flush = torch.zeros(128 * 1024 * 1024, dtype=torch.float32, device=dev)
     # configs[1]: 6040 users x 31 variants, K = 20, all phase-1 metrics (15 MB: launch/latency-bound)
     cfg = pipeline.PipelineConfig(list_len=20)

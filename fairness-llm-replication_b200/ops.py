@@ -119,6 +119,16 @@ def list_metrics(neutral, neutral_len, lists, lens, *, vocab: int, k_cap: Option
     return ListMetrics(inter, union, jac, serp, prag, sums, status, min(k_cap, K))
 
 
+def list_metrics_counts(neutral, neutral_len, lists, lens, *, vocab: int, k_cap: int, out_inter, out_union) -> None:
+    """The lean form behind the string API: exact |A & B| and |A | B| only, written into caller-provided
+    int32 views; no ratios, no sums, no status word, nothing allocated beyond the cached workspace."""
+    U, V, K = lists.shape
+    ws = _workspace(lists.device, _lib.load().flr_list_metrics_scratch_bytes(U, V, K, vocab))
+    _lib.call("flr_list_metrics", _ptr(neutral), _ptr(neutral_len), _ptr(lists), _ptr(lens), U, V, K, int(k_cap),
+              int(vocab), EMPTY_BOTH_IS_ONE, 0, _ptr(out_inter), _ptr(out_union), None, None, None, None, None,
+              _ptr(ws), ws.numel(), _stream())
+
+
 def list_metrics_kernel_name(V: int, K: int, vocab: int, k_cap: Optional[int] = None, rank_metrics: bool = True) -> str:
     """Name of the kernel ``list_metrics`` launches for a shape (the plan of csrc/list_metrics.cu:make_plan),
     for labelling measurements: what ncu and the profiler list is this name."""

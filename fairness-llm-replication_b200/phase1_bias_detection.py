@@ -10,13 +10,13 @@ import numpy as np
 from . import utils
 
 
-def measure_individual_fairness(profiles: List[Dict], recommendations: Dict[str, Dict]) -> Tuple[float, Dict]:
+def measure_individual_fairness(profiles: List[Dict], recommendations: Dict[str, Dict], _encoded=None) -> Tuple[float, Dict]:
     """Individual fairness over one-attribute counterfactual pairs -- reference:
     src/phase1_bias_detection.py:220-239 (same keys in the returned dict; population std)."""
     pairs = utils.create_profile_pairs(profiles)
     recs_dict = {r["profile_id"]: r["recommendations"]
                  for r in recommendations.values() if "recommendations" in r}
-    fairness_score, similarities = utils.calculate_individual_fairness(pairs, recs_dict)
+    fairness_score, similarities = utils.calculate_individual_fairness(pairs, recs_dict, _encoded=_encoded)
     return fairness_score, {
         "similarity_scores": similarities,
         "num_pairs": len(pairs),
@@ -25,9 +25,9 @@ def measure_individual_fairness(profiles: List[Dict], recommendations: Dict[str,
     }
 
 
-def measure_demographic_parity(recommendations_by_group) -> Tuple[float, Dict]:
+def measure_demographic_parity(recommendations_by_group, _encoded=None) -> Tuple[float, Dict]:
     """Demographic parity across groups -- reference: src/phase1_bias_detection.py:214-218."""
-    return utils.calculate_demographic_parity(recommendations_by_group)
+    return utils.calculate_demographic_parity(recommendations_by_group, _encoded=_encoded)
 
 
 # src/phase1_bias_detection.py:248-252: the reference's fixed set of "qualified" (acclaimed) titles
@@ -38,10 +38,11 @@ QUALIFIED_MOVIES = {
 }
 
 
-def measure_equal_opportunity(recommendations_by_group, movies=None) -> Tuple[float, Dict]:
+def measure_equal_opportunity(recommendations_by_group, movies=None, _encoded=None) -> Tuple[float, Dict]:
     """Equal opportunity against the reference's fixed qualified set -- reference:
     src/phase1_bias_detection.py:241-263 (``movies`` is accepted and unused there too)."""
-    opportunity_score, scores_by_group = utils.calculate_equal_opportunity(recommendations_by_group, QUALIFIED_MOVIES)
+    opportunity_score, scores_by_group = utils.calculate_equal_opportunity(recommendations_by_group, QUALIFIED_MOVIES,
+                                                                           _encoded=_encoded)
     return opportunity_score, {
         'opportunity_by_group': scores_by_group,
         'variance': np.var(list(scores_by_group.values())),
@@ -54,17 +55,21 @@ def calculate_phase1_metrics(profiles: List[Dict], all_recommendations: Dict[str
     """Step "[6/6] Calculating fairness metrics" of run_phase1 -- reference:
     src/phase1_bias_detection.py:343-405: group the lists by gender and by age, then demographic
     parity (both groupings), individual fairness and equal opportunity (gender grouping).  Returns the
-    ``'metrics'`` block of phase1_results.json.  Every number comes from the GPU path."""
+    ``'metrics'`` block of phase1_results.json.  Every number comes from the GPU path.  The lists are
+    encoded and uploaded once (``encode.EncodedRecommendations``) and shared by the four metrics."""
+    from . import encode
+    enc = encode.EncodedRecommendations([r['recommendations'] for r in all_recommendations.values()
+                                         if 'recommendations' in r])
     recs_by_gender, recs_by_age = defaultdict(list), defaultdict(list)
     for profile in profiles:
         pid = profile['id']
         if pid in all_recommendations and 'recommendations' in all_recommendations[pid]:
             recs_by_gender[profile['gender']].append(all_recommendations[pid]['recommendations'])
             recs_by_age[profile['age']].append(all_recommendations[pid]['recommendations'])
-    dp_gender_score, dp_gender_details = measure_demographic_parity(dict(recs_by_gender))
-    dp_age_score, dp_age_details = measure_demographic_parity(dict(recs_by_age))
-    if_score, if_details = measure_individual_fairness(profiles, all_recommendations)
-    eo_score, eo_details = measure_equal_opportunity(dict(recs_by_gender), movies)
+    dp_gender_score, dp_gender_details = measure_demographic_parity(dict(recs_by_gender), _encoded=enc)
+    dp_age_score, dp_age_details = measure_demographic_parity(dict(recs_by_age), _encoded=enc)
+    if_score, if_details = measure_individual_fairness(profiles, all_recommendations, _encoded=enc)
+    eo_score, eo_details = measure_equal_opportunity(dict(recs_by_gender), movies, _encoded=enc)
     return {
         'demographic_parity': {'gender': {'score': dp_gender_score, 'details': dp_gender_details},
                                'age': {'score': dp_age_score, 'details': dp_age_details}},

@@ -28,24 +28,38 @@ def _device() -> torch.device:
 
 
 def pair_set_counts(lists_a: Sequence[Sequence[Hashable]], lists_b: Sequence[Sequence[Hashable]],
-                    k_cap: Optional[int] = None) -> Tuple[np.ndarray, np.ndarray]:
+                    k_cap: Optional[int] = None, encoded: Optional[encode.EncodedRecommendations] = None
+                    ) -> Tuple[np.ndarray, np.ndarray]:
     """|set(a[:k]) & set(b[:k])| and |set(a[:k]) | set(b[:k])| for aligned list pairs, on the GPU.
-    Returns two int64 numpy arrays."""
+    Returns two int64 numpy arrays.  ``encoded``: lists already on the device
+    (``encode.EncodedRecommendations``); only their row indices travel.  One upload, one kernel
+    launch, one read-back per call."""
     P = len(lists_a)
     if P == 0:
         return np.zeros(0, np.int64), np.zeros(0, np.int64)
-    a, la, b, lb, vocab = encode.encode_pair_lists(lists_a, lists_b)
     dev = _device()
-    K = a.shape[1]
-    ta = torch.from_numpy(a).to(dev)
-    tla = torch.from_numpy(la).to(dev)
-    tb = torch.from_numpy(b).to(dev).view(P, 1, K)
-    tlb = torch.from_numpy(lb).to(dev).view(P, 1)
-    res = ops.list_metrics(ta, tla, tb, tlb, vocab=vocab, k_cap=K if k_cap is None else min(int(k_cap), K),
-                           rank_metrics=False, want_union=True, want_sums=False)
-    inter = res.inter.view(P).cpu().numpy().astype(np.int64)
-    union = res.union.view(P).cpu().numpy().astype(np.int64)
-    return inter, union
+    ia = ib = None
+    if encoded is not None:
+        ia, ib = encoded.rows_of(lists_a), encoded.rows_of(lists_b)
+    counts = torch.empty((2, P), dtype=torch.int32, device=dev)
+    if ia is None or ib is None:
+        # lists not seen before: encode them now; rows are gathered on the host and everything the kernel
+        # needs goes up in ONE copy
+        enc = encode.EncodedRecommendations(list(lists_a) + list(lists_b))
+        seq = np.array(enc.input_rows, dtype=np.int64)
+        K = enc.table.shape[1]
+        packed = np.concatenate([enc.table[seq].reshape(-1), enc.lens[seq]])
+        d = torch.from_numpy(packed).to(dev)
+        rows, rlen, vocab = d[:2 * P * K].view(2 * P, K), d[2 * P * K:], enc.vocab_size
+    else:
+        table, lens = encoded.on_device(dev)
+        K = table.shape[1]
+        idx = torch.from_numpy(np.concatenate([ia, ib])).to(dev)
+        rows, rlen, vocab = table.index_select(0, idx), lens.index_select(0, idx), encoded.vocab_size
+    ops.list_metrics_counts(rows[:P], rlen[:P], rows[P:].view(P, 1, K), rlen[P:].view(P, 1), vocab=vocab,
+                            k_cap=K if k_cap is None else min(int(k_cap), K), out_inter=counts[0], out_union=counts[1])
+    host = counts.cpu().numpy().astype(np.int64)
+    return host[0], host[1]
 
 
 def jaccard_from_counts(inter: np.ndarray, union: np.ndarray, both_empty: float) -> List[float]:
@@ -57,7 +71,8 @@ def jaccard_from_counts(inter: np.ndarray, union: np.ndarray, both_empty: float)
 
 
 def calculate_individual_fairness(profile_pairs: List[Tuple[str, str]],
-                                  recommendations: Dict[str, List[str]]) -> Tuple[float, List[float]]:
+                                  recommendations: Dict[str, List[str]],
+                                  _encoded: Optional[encode.EncodedRecommendations] = None) -> Tuple[float, List[float]]:
     """Mean pairwise Jaccard similarity -- reference: src/utils.py:217-244.
 
     Pairs with a pid missing from ``recommendations`` are skipped (:225-226); two empty lists
@@ -65,7 +80,7 @@ def calculate_individual_fairness(profile_pairs: List[Tuple[str, str]],
     """
     kept = [(p, q) for p, q in profile_pairs if p in recommendations and q in recommendations]
     inter, union = pair_set_counts([recommendations[p] for p, _ in kept],
-                                   [recommendations[q] for _, q in kept])
+                                   [recommendations[q] for _, q in kept], encoded=_encoded)
     similarity_scores = jaccard_from_counts(inter, union, 1.0)
     fairness_score = np.mean(similarity_scores) if similarity_scores else 0.0
     return fairness_score, similarity_scores
@@ -108,7 +123,8 @@ def create_profile_pairs(profiles: List[Dict], differing_attribute: Optional[str
 
 
 def calculate_demographic_parity(recommendations_by_group: Dict[str, List[List[str]]],
-                                 genre_mapping: Optional[Dict[str, List[str]]] = None) -> Tuple[float, Dict]:
+                                 genre_mapping: Optional[Dict[str, List[str]]] = None,
+                                 _encoded: Optional[encode.EncodedRecommendations] = None) -> Tuple[float, Dict]:
     """Demographic parity -- reference: src/utils.py:172-215 (``genre_mapping`` is accepted and unused
     there too).
 
@@ -119,9 +135,8 @@ def calculate_demographic_parity(recommendations_by_group: Dict[str, List[List[s
     The distances agree with the reference to ~1e-15 relative: the reference itself sums in the
     arbitrary order of a Python ``set`` of titles.
     """
-    names, vocab, hist = _group_histogram(recommendations_by_group)
+    names, items, index_of, hist = _group_histogram(recommendations_by_group, _encoded)
     G = len(names)
-    items = list(vocab.index.keys())
     counts = np.zeros((G, max(len(items), 1)), np.int64)
     divergences: List[float] = []
     if hist is not None:
@@ -132,7 +147,8 @@ def calculate_demographic_parity(recommendations_by_group: Dict[str, List[List[s
     distributions = {}
     for g, name in enumerate(names):
         total = int(counts[g].sum())
-        distributions[name] = ({items[x]: int(c) / total for x, c in enumerate(counts[g].tolist()) if c}
+        nz = np.flatnonzero(counts[g])
+        distributions[name] = ({items[x]: int(c) / total for x, c in zip(nz.tolist(), counts[g][nz].tolist())}
                                if total > 0 else {})
     avg_divergence = np.mean(divergences) if divergences else 0
     parity_score = 1 - avg_divergence
@@ -140,29 +156,50 @@ def calculate_demographic_parity(recommendations_by_group: Dict[str, List[List[s
                           "avg_divergence": avg_divergence}
 
 
-def _group_histogram(recommendations_by_group):
-    """(group names, item vocabulary, int64 [G, vocab] occurrence counts on the GPU or None if no rows)."""
-    vocab = encode.Vocabulary()
+def _group_histogram(recommendations_by_group, encoded: Optional[encode.EncodedRecommendations] = None):
+    """(group names, items in id order, item -> id lookup, int64 [G, vocab] occurrence counts on the GPU or
+    None if there are no rows).  With ``encoded`` the lists are already on the device and only
+    (row, group) indices are sent; otherwise the lists of this call are encoded first."""
     names = list(recommendations_by_group.keys())
-    rows, row_group = [], []
-    for g, name in enumerate(names):
-        for recs in recommendations_by_group[name]:
-            rows.append(vocab.encode(recs))
-            row_group.append(g)
     if len(names) > 256:
         raise ValueError("more than 256 groups are not supported on the GPU path")
-    if not rows:
-        return names, vocab, None
+    lists, row_group = [], []
+    for g, name in enumerate(names):
+        for recs in recommendations_by_group[name]:
+            lists.append(recs)
+            row_group.append(g)
+    rows = encoded.rows_of(lists) if encoded is not None else None
+    if rows is None:
+        encoded = encode.EncodedRecommendations(lists)
+        rows = encoded.rows_of(lists)
+    items = encoded.items
+    index_of = _ItemIndex(items)
+    if not lists:
+        return names, items, index_of, None
     dev = _device()
-    ids, lens = encode.pack_rows(rows)
-    hist = ops.group_item_histogram(torch.from_numpy(ids).to(dev), torch.from_numpy(lens).to(dev),
-                                    vocab=max(len(vocab), 1), n_groups=len(names),
-                                    groups=torch.from_numpy(np.asarray(row_group, np.uint8)).to(dev))
-    return names, vocab, hist
+    table, lens = encoded.on_device(dev)
+    sel = torch.from_numpy(np.concatenate([rows, np.asarray(row_group, np.int64)])).to(dev)
+    R = len(lists)
+    hist = ops.group_item_histogram(table.index_select(0, sel[:R]), lens.index_select(0, sel[:R]),
+                                    vocab=encoded.vocab_size, n_groups=len(names), groups=sel[R:].to(torch.uint8))
+    return names, items, index_of, hist
+
+
+class _ItemIndex:
+    """item -> id, built on first use (equal opportunity looks up a handful of titles)."""
+
+    def __init__(self, items):
+        self._items, self._index = items, None
+
+    def get(self, item):
+        if self._index is None:
+            self._index = {x: i for i, x in enumerate(self._items)}
+        return self._index.get(item)
 
 
 def calculate_equal_opportunity(recommendations_by_group: Dict[str, List[List[str]]],
-                                relevant_items: set) -> Tuple[float, Dict[str, float]]:
+                                relevant_items: set,
+                                _encoded: Optional[encode.EncodedRecommendations] = None) -> Tuple[float, Dict[str, float]]:
     """Equal opportunity -- reference: src/utils.py:246-275.
 
     Per group: distinct relevant items recommended / recommendations made (0.0 for a group without
@@ -170,18 +207,19 @@ def calculate_equal_opportunity(recommendations_by_group: Dict[str, List[List[st
     counts per group come from the GPU; the ratios, ``np.var`` and the final expression are the
     reference's own, so the result is bit-identical.
     """
-    names, vocab, hist = _group_histogram(recommendations_by_group)
+    names, _, index_of, hist = _group_histogram(recommendations_by_group, _encoded)
     opportunity_scores: Dict[str, float] = {}
     if hist is None:
         opportunity_scores = {name: 0.0 for name in names}
     else:
         flags = np.zeros(hist.shape[1], np.uint8)
         for item in relevant_items:
-            i = vocab.index.get(item)
+            i = index_of.get(item)
             if i is not None:
                 flags[i] = 1
         rel, tot = ops.equal_opportunity_counts(hist, torch.from_numpy(flags).to(hist.device))
-        for name, r, n in zip(names, rel.cpu().tolist(), tot.cpu().tolist()):
+        both = torch.stack([rel, tot]).cpu().tolist()            # one read-back
+        for name, r, n in zip(names, both[0], both[1]):
             opportunity_scores[name] = r / n if n > 0 else 0.0
     scores = list(opportunity_scores.values())
     variance = np.var(scores) if scores else 0
