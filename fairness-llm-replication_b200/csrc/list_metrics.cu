@@ -949,7 +949,7 @@ __global__ void __launch_bounds__(CMP_THREADS) list_metrics_cmp_kernel(const LmP
         int n_a = 0;
         for (int i = 0; i < Ka; ++i) {
             const int x = A[i];
-            if (check_vocab && static_cast<unsigned>(x) >= vocab) { ++oov; continue; }
+            if (check_vocab && static_cast<unsigned>(x) >= vocab) { oov += (pair % V == 0); continue; }   // once per user, like the table kernels
             bool dup = false;
             for (int i2 = 0; i2 < i; ++i2) dup |= (A[i2] == x);
             n_a += !dup;
@@ -1265,8 +1265,18 @@ extern "C" int flr_list_metrics_static(const int32_t *neutral, const int32_t *ne
                         rank_metrics);
     if (rc != FLR_OK) return rc;
 
-    // How many partials this shape writes: 4 doubles per thread of the kernel that will run.
-    const Plan pl = make_plan(U, V, K, k_cap, vocab);
+    // How many partials this shape writes: 4 doubles per thread of the kernel that will run.  The compare
+    // kernel walks its pairs with a grid stride, so its grid can be cut down to what the array holds (a
+    // multiple of V blocks, so that a thread still sees one variant only).
+    Plan pl = make_plan(U, V, K, k_cap, vocab);
+    if (!pl.table) {
+        const int64_t room = static_cast<int64_t>(FLR_LIST_METRICS_STATIC_SCRATCH_BYTES) / (CMP_THREADS * 4 * sizeof(double));
+        const int64_t blocks = std::min<int64_t>(pl.grid, (room / V) * V);
+        if (blocks >= V) {
+            pl.grid = static_cast<int>(blocks);
+            pl.cmp_threads = blocks * CMP_THREADS;
+        }
+    }
     const size_t need = partial_bytes(pl);
     FLR_REQUIRE(need <= static_cast<size_t>(FLR_LIST_METRICS_STATIC_SCRATCH_BYTES), FLR_E_UNSUPPORTED,
                 "list_metrics_static: this shape needs %zu bytes of partial sums but the built-in scratch holds "

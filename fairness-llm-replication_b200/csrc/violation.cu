@@ -21,6 +21,14 @@ __global__ void threshold_schedule_kernel(const float *__restrict__ q0, const un
     const unsigned long long n = state[FLR_ST_N], less = state[FLR_ST_LESS], eq = state[FLR_ST_EQUAL];
     const bool any_above = state[FLR_ST_EMPTY] == 0ull && n > less + eq;
     float q = q0[0];
+    // The closed form needs q0 >= 0: then gamma * q never exceeds q, and a floor above q0 is reached in one
+    // step and kept whatever the later counts are.  For q0 < 0 (scores may be negative in general; the
+    // cosine scores never are) gamma * q0 rises above q0 and the recurrence depends on counts this kernel
+    // does not have: every threshold is written as NaN, which flags nothing and cannot pass for a result.
+    if (any_above && q < 0.f) {
+        for (int r = 0; r <= rounds; ++r) out_thr[r] = __int_as_float(0x7fc00000);
+        return;
+    }
     for (int r = 0; r < rounds; ++r) {
         out_thr[r] = q;
         if (any_above) q = fmaxf(__fmul_rn(gamma, q), q_min);

@@ -343,8 +343,7 @@ def ndcg(rel, rel_len, ideal, ideal_len, k: int) -> torch.Tensor:
     out = torch.empty(B, dtype=torch.float64, device=rel.device)
     _lib.call("flr_ndcg", _ptr(rel), _ptr(rel_len), n, _ptr(ideal), _ptr(ideal_len), m, int(k), _ptr(log2tab), B,
               _ptr(out), _stream())
-    torch.cuda.current_stream().synchronize()         # log2tab is released on return
-    return out
+    return out            # log2tab goes back to torch's stream-ordered allocator: reuse is ordered after this launch
 
 
 def exposure_by_group(group, lens, n_groups: int):
@@ -359,8 +358,7 @@ def exposure_by_group(group, lens, n_groups: int):
     cnt = torch.empty((B, n_groups), dtype=torch.int32, device=group.device)
     _lib.call("flr_exposure_by_group", _ptr(group), _ptr(lens), n, int(n_groups), _ptr(weight), B, _ptr(mean), _ptr(cnt),
               _stream())
-    torch.cuda.current_stream().synchronize()         # weight is released on return
-    return mean, cnt
+    return mean, cnt      # (weight: same stream-ordered release as in ndcg)
 
 
 # ------------------------------------------------------------------------------ config 4

@@ -63,7 +63,8 @@ int         flr_device_info(int *sm_count, int *cc_major, int *cc_minor);
  * Outputs (any may be NULL): out_inter/out_union int32 [U,V] (exact), out_jac/out_serp/
  * out_prag float [U,V], out_variant_sums double [V,4] = per variant {sum jaccard, sum
  * serp_num, sum prag_num, user count} (summed in a fixed order: bit-reproducible).
- * out_status int32 [1]: number of ids found outside [0, vocab) (such ids are skipped).
+ * out_status int32 [1]: number of ids found outside [0, vocab) (such ids are skipped): counted per
+ * list row, a neutral row once per user.
  * ------------------------------------------------------------------------------------- */
 size_t flr_list_metrics_scratch_bytes(int64_t U, int V, int K, int vocab);
 int flr_list_metrics(const int32_t *neutral, const int32_t *neutral_len,
@@ -90,7 +91,9 @@ int flr_list_metrics(const int32_t *neutral, const int32_t *neutral_len,
  *   - a shape whose partial sums do not fit the array is refused with FLR_E_UNSUPPORTED and a
  *     message naming both sizes.  Shapes served by the table kernel (2 <= V <= 128,
  *     vocab <= 16384, k_cap <= 64) always fit on a B200, whatever U is; compare-kernel shapes
- *     (V = 1 pair lists, larger vocabularies) fit up to about 65,000 pairs;
+ *     (V = 1 pair lists, larger vocabularies) are run with as many thread blocks as the array has
+ *     room for (each thread then walks more pairs), so they fit for any U as long as V blocks do
+ *     (V <= 512);
  *   - the first call on a device looks up the array's device address
  *     (cudaGetSymbolAddress, with that device current); make that first call before any stream
  *     capture starts;
@@ -169,7 +172,10 @@ int flr_select_scan(int dtype, int G, int pass, double one_minus_alpha,
  *
  * flr_threshold_schedule: thr[0] = q0[0]; thr[r+1] = max(fl32(gamma*thr[r]), q_min) when
  *   the select state says some score lies above q0 (n - less - equal > 0), else thr[r].
- *   Valid closed form of the round recurrence for 0 < gamma <= 1 and q0 >= 0.
+ *   Valid closed form of the round recurrence for 0 < gamma <= 1 and q0 >= 0.  When some score lies
+ *   above q0 and q0 < 0, the recurrence depends on per-round counts this call does not have: every
+ *   out_thr entry is written as NaN (a NaN threshold flags nothing), so the unsupported case cannot
+ *   pass for a result.
  *   q0: float [1] (device), state: the select state of group 0, out_thr: float [rounds+1].
  * flr_violation_detect: flags[i] bit r = scores[i] > thr[r]; counts[r] += #flags (uint64,
  *   added to; caller zeroes), variant_counts[v*rounds + r] likewise for v = i % V (nullable).

@@ -139,6 +139,10 @@ def test_schedule_and_violation_match_round_recurrence():
         assert np.array_equal(vcounts.cpu().numpy(), want["variant_counts"])
     with pytest.raises(ops._lib.FlrError):
         ops.threshold_schedule(thr0, state, gamma=1.5)
+    # a negative order statistic with scores above it: the closed form does not hold, NaN says so
+    neg = torch.from_numpy((s - 1.0).astype(np.float32)).cuda()
+    thr0, state = ops.radix_select(neg, alpha=0.1)
+    assert bool(torch.isnan(ops.threshold_schedule(thr0, state, rounds=R)).all())
 
 
 def test_violation_small_and_odd_sizes():

@@ -113,6 +113,32 @@ def test_out_of_vocab_ids_are_counted_and_skipped():
     assert res.union.cpu().tolist() == [[4, 5]]
 
 
+@pytest.mark.parametrize("V,K,vocab", [(31, 20, 3706), (8, 12, 3706), (31, 20, 20000), (3, 64, 50)])
+def test_foreign_ids_in_the_neutral_list_count_once_per_user(V, K, vocab):
+    """Ids outside [0, vocab) are skipped wherever they stand and counted once per list row: a neutral row
+    belongs to the user, not to each of its V pairs.  Every kernel family (warp, register, table, compare)
+    must report the same number for the same input."""
+    rng = np.random.default_rng(V + K)
+    U = 97
+    neutral, nlen, lists, lens = _random_case(rng, U, V, K, min(vocab, 60))
+    bad_n = rng.random((U, K)) < 0.07
+    bad_l = rng.random((U, V, K)) < 0.03
+    neutral = np.where(bad_n, vocab + rng.integers(0, 5, (U, K)), neutral).astype(np.int32)
+    lists = np.where(bad_l, -1 - rng.integers(0, 5, (U, V, K)), lists).astype(np.int32)
+    res = _run(neutral, nlen, lists, lens, vocab=vocab)
+    in_n = np.arange(K)[None, :] < nlen[:, None]
+    in_l = np.arange(K)[None, None, :] < lens[:, :, None]
+    expect = int((bad_n & in_n).sum() + (bad_l & in_l).sum())
+    assert int(res.status.item()) == expect
+    inter, union = res.inter.cpu().numpy(), res.union.cpu().numpy()
+    ok = lambda x: 0 <= x < vocab
+    for u in range(U):
+        a = {int(x) for x in neutral[u, :nlen[u]] if ok(x)}
+        for v in range(V):
+            b = {int(x) for x in lists[u, v, :lens[u, v]] if ok(x)}
+            assert inter[u, v] == len(a & b) and union[u, v] == len(a | b)
+
+
 def test_tail_tiles_and_tiny_inputs():
     rng = np.random.default_rng(12)
     for U in (1, 2, 3, 4, 5, 7, 9, 301):

@@ -89,13 +89,59 @@ def test_static_scratch_entry_matches_regular_entry_twice_in_a_row():
         _same(again, want, s["rank"])
 
 
-def test_static_scratch_entry_refuses_shapes_beyond_its_array():
-    """A compare-kernel shape with more pairs than the built-in array can hold partials for is
-    turned down with a message that names both sizes -- the host is told to use the entry point
-    that takes caller-provided scratch; nothing is launched."""
+def test_static_scratch_entry_matches_the_oracle():
+    """The no-scratch entry point against the CPU oracle directly (not only against its sibling):
+    exact intersections, unions and integer sums, ratios within 1e-6."""
+    from oracle import np_oracle as O
+    U, V, K, vocab = 1201, 31, 50, 3706
+    tensors = _inputs(11, U, V, K, vocab)
+    got = _call(True, tensors, U, V, K, vocab, K, 1, 1)
+    neutral, nlen, lists, lens = (t.cpu().numpy() for t in tensors)
+    want = O.list_metrics(neutral, nlen, lists, lens, k_cap=K, empty_policy=1)
+    assert np.array_equal(got["inter"].cpu().numpy(), want["inter"])
+    assert np.array_equal(got["union"].cpu().numpy(), want["union"])
+    np.testing.assert_allclose(got["serp"].cpu().numpy(), want["serp"], rtol=RTOL, atol=0)
+    np.testing.assert_allclose(got["prag"].cpu().numpy(), want["prag"], rtol=RTOL, atol=0)
+    sums = got["sums"].cpu().numpy()
+    assert np.array_equal(sums[:, 1], want["serp_num"].sum(0)) and np.array_equal(sums[:, 2], want["prag_num"].sum(0))
+    np.testing.assert_allclose(sums[:, 0], want["jaccard"].sum(0), rtol=1e-12)
+
+
+def test_static_scratch_entry_allocates_nothing():
+    """What the entry point is for: once the first call on the device has looked up the array's address,
+    further calls leave the device's free memory and torch's allocator untouched."""
+    from fairness_llm_replication_b200 import _lib
+    U, V, K, vocab = 4000, 31, 20, 3706
+    tensors = _inputs(12, U, V, K, vocab)
+    o = _outputs(U, V)
+    p = lambda t: C.c_void_p(t.data_ptr())
+    stream = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    args = [p(t) for t in tensors] + [U, V, K, K, vocab, 1, 1, p(o["inter"]), p(o["union"]), p(o["jac"]), p(o["serp"]),
+                                      p(o["prag"]), p(o["sums"]), p(o["status"]), stream]
+    _lib.call("flr_list_metrics_static", *args)          # first call: address look-up, module load
+    torch.cuda.synchronize()
+    free0, _ = torch.cuda.mem_get_info()
+    stats0 = torch.cuda.memory_stats()
+    for _ in range(5):
+        _lib.call("flr_list_metrics_static", *args)
+    torch.cuda.synchronize()
+    free1, _ = torch.cuda.mem_get_info()
+    stats1 = torch.cuda.memory_stats()
+    assert free1 == free0
+    for key in ("allocation.all.allocated", "segment.all.allocated", "reserved_bytes.all.current"):
+        assert stats1.get(key) == stats0.get(key)
+
+
+def test_static_scratch_entry_serves_large_compare_shapes_and_refuses_what_cannot_fit():
+    """Compare-kernel shapes (V = 1 pair lists of the string API) run with as many blocks as the array has
+    room for, whatever the number of pairs; a shape whose first V blocks alone overflow the array is turned
+    down with a message that names both sizes, and nothing is launched."""
     from fairness_llm_replication_b200 import _lib
     U, V, K, vocab = 200_000, 1, 8, 500
     tensors = _inputs(4, U, V, K, vocab)
+    _same(_call(True, tensors, U, V, K, vocab, K, 1, 0), _call(False, tensors, U, V, K, vocab, K, 1, 0), 0)
+    U, V, K, vocab = 3, 600, 4, 100000          # 600 blocks x 128 threads x 32 B > 2 MiB
+    tensors = _inputs(6, U, V, K, vocab)
     with pytest.raises(_lib.FlrError) as err:
         _call(True, tensors, U, V, K, vocab, K, 1, 0)
     assert err.value.code == _lib.E_UNSUPPORTED
