@@ -12,14 +12,29 @@ from . import utils
 
 def measure_individual_fairness(profiles: List[Dict], recommendations: Dict[str, Dict], _encoded=None) -> Tuple[float, Dict]:
     """Individual fairness over one-attribute counterfactual pairs -- reference:
-    src/phase1_bias_detection.py:220-239 (same keys in the returned dict; population std)."""
-    pairs = utils.create_profile_pairs(profiles)
-    recs_dict = {r["profile_id"]: r["recommendations"]
-                 for r in recommendations.values() if "recommendations" in r}
-    fairness_score, similarities = utils.calculate_individual_fairness(pairs, recs_dict, _encoded=_encoded)
+    src/phase1_bias_detection.py:220-239 (same keys in the returned dict; population std).
+
+    Same pairs, same order and the same float64 arithmetic as the reference, but nothing here is per-pair
+    Python: the pairs stay index arrays (``utils.profile_pair_indices``), a pair is kept when both profile
+    ids have a list (src/utils.py:225-226), and the kept pairs go to the GPU as row indices into the
+    encoded lists."""
+    from . import encode
+    recs = [r for r in recommendations.values() if "recommendations" in r]
+    keys = [r["profile_id"] for r in recs]
+    lists = [r["recommendations"] for r in recs]
+    if _encoded is None or _encoded.rows_of(lists) is None:
+        _encoded = encode.EncodedRecommendations(lists)
+    row_of_pid = dict(zip(keys, _encoded.rows_of(lists).tolist()))      # a repeated profile_id: the last one wins, as in a dict
+    prof_row = np.fromiter((row_of_pid.get(p["id"], -1) for p in profiles), dtype=np.int64, count=len(profiles))
+    ii, jj = utils.profile_pair_indices(profiles)
+    ra, rb = prof_row[ii], prof_row[jj]
+    keep = (ra >= 0) & (rb >= 0)
+    inter, union = utils.pair_set_counts_rows(_encoded, ra[keep], rb[keep])
+    similarities = utils.jaccard_from_counts(inter, union, 1.0)
+    fairness_score = np.mean(similarities) if similarities else 0.0
     return fairness_score, {
         "similarity_scores": similarities,
-        "num_pairs": len(pairs),
+        "num_pairs": int(len(ii)),
         "mean_similarity": fairness_score,
         "std_similarity": np.std(similarities) if similarities else 0,
     }

@@ -52,11 +52,27 @@ def pair_set_counts(lists_a: Sequence[Sequence[Hashable]], lists_b: Sequence[Seq
         d = torch.from_numpy(packed).to(dev)
         rows, rlen, vocab = d[:2 * P * K].view(2 * P, K), d[2 * P * K:], enc.vocab_size
     else:
-        table, lens = encoded.on_device(dev)
-        K = table.shape[1]
-        idx = torch.from_numpy(np.concatenate([ia, ib])).to(dev)
-        rows, rlen, vocab = table.index_select(0, idx), lens.index_select(0, idx), encoded.vocab_size
+        return pair_set_counts_rows(encoded, ia, ib, k_cap)
     ops.list_metrics_counts(rows[:P], rlen[:P], rows[P:].view(P, 1, K), rlen[P:].view(P, 1), vocab=vocab,
+                            k_cap=K if k_cap is None else min(int(k_cap), K), out_inter=counts[0], out_union=counts[1])
+    host = counts.cpu().numpy().astype(np.int64)
+    return host[0], host[1]
+
+
+def pair_set_counts_rows(encoded: encode.EncodedRecommendations, rows_a: np.ndarray, rows_b: np.ndarray,
+                         k_cap: Optional[int] = None) -> Tuple[np.ndarray, np.ndarray]:
+    """``pair_set_counts`` for lists that are already on the device: pair p compares rows ``rows_a[p]`` and
+    ``rows_b[p]`` of ``encoded``.  Only the two index arrays go up and the two count arrays come back."""
+    P = len(rows_a)
+    if P == 0:
+        return np.zeros(0, np.int64), np.zeros(0, np.int64)
+    dev = _device()
+    table, lens = encoded.on_device(dev)
+    K = table.shape[1]
+    idx = torch.from_numpy(np.concatenate([rows_a, rows_b]).astype(np.int64, copy=False)).to(dev)
+    rows, rlen = table.index_select(0, idx), lens.index_select(0, idx)
+    counts = torch.empty((2, P), dtype=torch.int32, device=dev)
+    ops.list_metrics_counts(rows[:P], rlen[:P], rows[P:].view(P, 1, K), rlen[P:].view(P, 1), vocab=encoded.vocab_size,
                             k_cap=K if k_cap is None else min(int(k_cap), K), out_inter=counts[0], out_union=counts[1])
     host = counts.cpu().numpy().astype(np.int64)
     return host[0], host[1]
@@ -93,9 +109,18 @@ def create_profile_pairs(profiles: List[Dict], differing_attribute: Optional[str
     Host logic (it decides which pairs are scored, it scores nothing).  The reference's
     double Python loop is replaced by blocked integer comparisons, so 10^5 profiles are usable.
     """
+    ii, jj = profile_pair_indices(profiles, differing_attribute)
+    ids = [p["id"] for p in profiles]
+    return [(ids[i], ids[j]) for i, j in zip(ii.tolist(), jj.tolist())]
+
+
+def profile_pair_indices(profiles: List[Dict], differing_attribute: Optional[str] = None) -> Tuple[np.ndarray, np.ndarray]:
+    """``create_profile_pairs`` as two int64 index arrays into ``profiles`` (same pairs, same order): what
+    a caller that goes on to score the pairs needs, without a Python tuple per pair."""
     n = len(profiles)
+    empty = np.zeros(0, np.int64)
     if n < 2:
-        return []
+        return empty, empty
     codes = np.zeros((len(_ATTRS), n), np.int64)
     for a, attr in enumerate(_ATTRS):
         table: Dict[Hashable, int] = {}
@@ -105,8 +130,7 @@ def create_profile_pairs(profiles: List[Dict], differing_attribute: Optional[str
             # 0 = attribute absent
     want = None if differing_attribute is None else (
         _ATTRS.index(differing_attribute) if differing_attribute in _ATTRS else -1)
-    ids = [p["id"] for p in profiles]
-    pairs: List[Tuple[str, str]] = []
+    out_i, out_j = [], []
     block = max(1, min(n, (1 << 24) // n))
     for s in range(0, n, block):
         e = min(n, s + block)
@@ -118,8 +142,9 @@ def create_profile_pairs(profiles: List[Dict], differing_attribute: Optional[str
             ok &= differs[want] if want >= 0 else False
         ok &= np.arange(n)[None, :] > np.arange(s, e)[:, None]     # j > i
         ii, jj = np.nonzero(ok)
-        pairs.extend((ids[s + i], ids[j]) for i, j in zip(ii.tolist(), jj.tolist()))
-    return pairs
+        out_i.append(ii + s)
+        out_j.append(jj)
+    return np.concatenate(out_i).astype(np.int64), np.concatenate(out_j).astype(np.int64)
 
 
 def calculate_demographic_parity(recommendations_by_group: Dict[str, List[List[str]]],

@@ -21,3 +21,21 @@ P1.calculate_phase1_metrics(profiles, allrecs); ts = []
 for _ in range(11):
     t0 = time.perf_counter(); P1.calculate_phase1_metrics(profiles, allrecs); ts.append(time.perf_counter() - t0)
 print(json.dumps({"case": "phase-1 metric step, 45 profiles", "impl": "ours", "ms": 1e3 * float(np.median(ts))}))
+
+# the whole phase-1 metric step on a results-file-sized input (as bench.py's other_configs does)
+titles = ["Title %d (19%02d)" % (i, i % 100) for i in range(300)]
+w = 1.0 / np.arange(1, 301)
+big_profiles = [{"id": "q%d" % i, "gender": g, "age": a, "occupation": "professional"}
+                for i, (g, a, _) in enumerate((g, a, r) for g in ("male", "female", "non-binary")
+                                              for a in ("18-24", "25-34", "35-44", "45-54", "55+") for r in range(67))]
+big_recs = {p["id"]: {"profile_id": p["id"], "recommendations":
+                      [titles[t] for t in rng.choice(300, size=10, replace=False, p=w / w.sum())]} for p in big_profiles}
+P1.calculate_phase1_metrics(big_profiles[:30], big_recs)
+ts = []
+for _ in range(5):
+    t0 = time.perf_counter(); m = P1.calculate_phase1_metrics(big_profiles, big_recs); ts.append(time.perf_counter() - t0)
+t0 = time.perf_counter(); ref = R.measure_individual_fairness(big_profiles, big_recs); t_port_if = time.perf_counter() - t0
+print(json.dumps({"case": "phase-1 metric step, 1005 profiles, %d pairs" % m["individual_fairness"]["details"]["num_pairs"],
+                  "ours_s": float(np.median(ts)), "port_individual_fairness_alone_s": t_port_if,
+                  "identical": bool(float(m["individual_fairness"]["score"]) == float(ref[0])
+                                    and m["individual_fairness"]["details"]["similarity_scores"] == ref[1]["similarity_scores"])}))
