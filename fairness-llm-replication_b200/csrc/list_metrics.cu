@@ -544,7 +544,7 @@ __global__ void __launch_bounds__(NT, 2) list_metrics_reg_kernel(const LmParams 
 //   4. redoes flagged rows (a repeat, or a foreign id: `vocab` stands for those and its bit is always
 //      set) with the exact sequential loop -- rare, one lane at a time, from a copy of the row in
 //      shared memory;
-//   5. writes the pair's results, wipes the bit sets and un-marks the table.
+//   5. writes the pair's results, un-sets the bits it set (one word store per id) and un-marks the table.
 // Positions past a row's length hold spare ids (vocab + 1 + position): private bits, table entries
 // that read "absent"; each one counts as a miss that follows every hit, which is subtracted at the end.
 // ---------------------------------------------------------------------------------------
@@ -743,6 +743,7 @@ __global__ void __launch_bounds__(NT, 2) list_metrics_warp_kernel(const LmParams
         char *bits_base = reinterpret_cast<char *>(s_bits + lane);
         uint32_t seen_lo = 0, seen_hi = 0;      // bit TOP - r = neutral rank r was hit
         uint32_t repeat = 0, absent_pos = 0;
+        uint32_t tpack = 0;
         int below = 0;
 #pragma unroll
         for (int j = 0; j < KT; ++j) {
@@ -752,7 +753,16 @@ __global__ void __launch_bounds__(NT, 2) list_metrics_warp_kernel(const LmParams
             const uint32_t old = atomicOr(wp, bit);
             repeat |= old & bit;
             const unsigned tt = tab[idx];                  // TOP - rank, TOP + 1 when absent
-            if constexpr (RANK) absent_pos += (tt >> ABSENT_SHIFT) * static_cast<unsigned>(j);
+            if constexpr (RANK) {
+                // four table bytes per register (a multiply-add each: the bytes are disjoint), then one masked
+                // byte dot product with the positions as weights: ABSENT * sum of the absent positions
+                tpack = (j & 3) == 0 ? tt : tt * (1u << (8 * (j & 3))) + tpack;
+                if ((j & 3) == 3 || j == KT - 1) {
+                    const unsigned j0 = static_cast<unsigned>(j & ~3);
+                    const unsigned wts = j0 | ((j0 + 1) << 8) | ((j0 + 2) << 16) | ((j0 + 3) << 24);
+                    absent_pos = __dp4a(tpack & (ABSENT * 0x01010101u), wts, absent_pos);
+                }
+            }
             if constexpr (NARROW) {
                 if constexpr (RANK) below += __popc(shr32_clamped(seen_lo, tt));    // hits so far ranked before this one (absent: 0)
                 seen_lo += shl32_clamped(1u, tt);                                    // absent: 0; bits of a clean row are distinct: + is |
@@ -769,6 +779,7 @@ __global__ void __launch_bounds__(NT, 2) list_metrics_warp_kernel(const LmParams
         // A clean row of Kb elements with hits at positions p_1 < ... < p_h: a miss counts the hits before
         // it, which adds up to h (Kb - 1) - sum p_i - h (h - 1) / 2; spares past the end count nothing.
         int inter = __popc(seen_lo) + __popc(seen_hi);
+        absent_pos >>= ABSENT_SHIFT;
         const int pos_sum = KT * (KT - 1) / 2 - static_cast<int>(absent_pos);
         int serp = inter * Kn - pos_sum;
         int prag = below + inter * (Kb - 1) - pos_sum - inter * (inter - 1) / 2;
@@ -854,18 +865,14 @@ __global__ void __launch_bounds__(NT, 2) list_metrics_warp_kernel(const LmParams
             acc_n += 1;
         }
 
-        // ---- wipe the warp's bit sets (128-bit stores; the last three rows each lane resets itself,
-        //      re-arming the foreign bit) and un-mark the rank table ----
+        // ---- un-set the bit sets and un-mark the rank table.  Every bit a lane set lives in the word of one of
+        //      its ids, so 50 conflict-free word stores per lane clear them all -- less than half the shared-
+        //      memory traffic of sweeping all 118 rows, which is what bounded the kernel ----
         __syncwarp();
         {
-            int4 *bits4 = reinterpret_cast<int4 *>(s_bits);
-            const int n4 = own_row * 8;
-            const int4 zero = make_int4(0, 0, 0, 0);
-#pragma unroll 8
-            for (int i = lane; i < n4; i += 32) bits4[i] = zero;
+#pragma unroll
+            for (int j = 0; j < KT; ++j) *reinterpret_cast<uint32_t *>(bits_base + (ids[j] & ~31u) * 4u) = 0u;
             s_bits[own_row * 32 + lane] = foreign_bit;
-            s_bits[(own_row + 1) * 32 + lane] = 0u;
-            s_bits[(own_row + 2) * 32 + lane] = 0u;
         }
         if (un_id0 < vocab) tab[un_id0] = static_cast<uint8_t>(ABSENT);
         if (un_id1 < vocab) tab[un_id1] = static_cast<uint8_t>(ABSENT);
