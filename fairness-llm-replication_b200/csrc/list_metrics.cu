@@ -1049,7 +1049,11 @@ Plan make_plan(int64_t U, int V, int K, int k_cap, int vocab) {
         const int cap = K <= 10 ? 10 : K <= 20 ? 20 : K <= 32 ? 32 : K <= 50 ? 50 : K <= 62 ? 62 : 0;   // unroll capacity
         const bool reg = cap != 0;
         const char *pick = getenv("FLR_LM_KERNEL");
-        if (reg && V >= 17 && V <= 32 && !(pick && pick[0] == 'r')) {
+        // the warp kernel's four per-warp regions must fit one SM (vocabularies up to ~9000 ids do; with more
+        // than half of it only one CTA is resident per SM); larger vocabularies fall through to the tile
+        // kernels and from there to the compare kernel
+        if (reg && V >= 17 && V <= 32 && !(pick && pick[0] == 'r') &&
+            wk_layout(V, K, cap, vocab).total <= static_cast<size_t>(226 * 1024)) {
             pl.table = true;
             pl.warp = true;
             pl.reg_k = cap;

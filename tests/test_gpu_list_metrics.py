@@ -65,6 +65,18 @@ def test_table_kernel_random(V, K):
         _check(*case, vocab=vocab, k_cap=K // 2)
 
 
+@pytest.mark.parametrize("V,K,vocab", [(17, 33, 3706), (24, 62, 3706), (29, 50, 200), (31, 32, 64), (20, 11, 5000), (31, 20, 8000), (32, 45, 16384)])
+def test_warp_kernel_shapes(V, K, vocab):
+    """The warp kernel's corners: idle lanes (V < 32), rows longer than one 32-wide half (K > 32), rows below
+    the unroll capacity (K between capacities), tiny vocabularies (nearly every row has a repeat and goes
+    through the exact warp-cooperative pass), the largest vocabulary the table kernels take."""
+    rng = np.random.default_rng(V * 1000 + K)
+    case = _random_case(rng, 131, V, K, min(vocab, 4 * K))
+    _check(*case, vocab=vocab)
+    _check(*case, vocab=vocab, empty_policy=0, k_cap=max(1, K - 7))
+    _check(*case, vocab=vocab, rank=False)
+
+
 @pytest.mark.parametrize("V,K,vocab", [(1, 10, 500), (1, 20, 100000), (3, 64, 50), (124, 20, 3706), (5, 12, 70000)])
 def test_compare_kernel_shapes(V, K, vocab):
     """V = 1 pair lists (string API), huge vocabularies and V > 128 go through the compare kernel."""
