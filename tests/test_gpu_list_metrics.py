@@ -77,6 +77,20 @@ def test_warp_kernel_shapes(V, K, vocab):
     _check(*case, vocab=vocab, rank=False)
 
 
+def test_random_shapes_against_the_oracle():
+    """Forty seeded random shapes across every kernel family (V 1..40, K 1..64, vocabularies from a few ids
+    to beyond the table kernels' limit, random lengths and k_cap, both empty-set conventions)."""
+    rng = np.random.default_rng(2024)
+    for _ in range(40):
+        V = int(rng.integers(1, 41))
+        K = int(rng.integers(1, 65))
+        vocab = int(rng.choice([max(2 * K, 8), 300, 3706, 9000, 20000]))
+        U = int(rng.integers(1, 90))
+        case = _random_case(rng, U, V, K, min(vocab, max(8, 3 * K)))
+        k_cap = None if rng.random() < 0.5 else int(rng.integers(1, K + 1))
+        _check(*case, vocab=vocab, k_cap=k_cap, empty_policy=int(rng.integers(0, 2)), rank=bool(rng.random() < 0.7))
+
+
 @pytest.mark.parametrize("V,K,vocab", [(1, 10, 500), (1, 20, 100000), (3, 64, 50), (124, 20, 3706), (5, 12, 70000)])
 def test_compare_kernel_shapes(V, K, vocab):
     """V = 1 pair lists (string API), huge vocabularies and V > 128 go through the compare kernel."""
