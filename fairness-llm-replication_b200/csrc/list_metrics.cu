@@ -741,6 +741,8 @@ __global__ void __launch_bounds__(NT, 2) list_metrics_warp_kernel(const LmParams
 
         // ---- optimistic pass over the row ----
         char *bits_base = reinterpret_cast<char *>(s_bits + lane);
+        const uint32_t tab32 = smem_u32(tab);
+        int below_hi = 0;                       // the two halves' popcounts go to two sums: adds the FMA pipe can take
         uint32_t seen_lo = 0, seen_hi = 0;      // bit TOP - r = neutral rank r was hit
         uint32_t repeat = 0, absent_pos = 0;
         uint32_t tpack = 0;
@@ -752,7 +754,8 @@ __global__ void __launch_bounds__(NT, 2) list_metrics_warp_kernel(const LmParams
             const uint32_t bit = 1u << (idx & 31u);
             const uint32_t old = atomicOr(wp, bit);
             repeat |= old & bit;
-            const unsigned tt = tab[idx];                  // TOP - rank, TOP + 1 when absent
+            unsigned tt;                                   // TOP - rank, TOP + 1 when absent
+            asm volatile("ld.shared.u8 %0, [%1];" : "=r"(tt) : "r"(tab32 + idx));   // one 32-bit base: a two-input add
             if constexpr (RANK) {
                 // four table bytes per register (a multiply-add each: the bytes are disjoint), then one masked
                 // byte dot product with the positions as weights: ABSENT * sum of the absent positions
@@ -769,7 +772,9 @@ __global__ void __launch_bounds__(NT, 2) list_metrics_warp_kernel(const LmParams
             } else {
                 if constexpr (RANK) {
                     const uint64_t seen = (static_cast<uint64_t>(seen_hi) << 32) | seen_lo;
-                    below += __popcll(shr64_clamped(seen, tt));
+                    const uint64_t sh = shr64_clamped(seen, tt);     // hits so far ranked before this one (absent: 0)
+                    below += __popc(static_cast<uint32_t>(sh));
+                    below_hi += __popc(static_cast<uint32_t>(sh >> 32));
                 }
                 const uint64_t own = shl64_clamped(1ull, tt);
                 seen_lo += static_cast<uint32_t>(own);
@@ -779,6 +784,7 @@ __global__ void __launch_bounds__(NT, 2) list_metrics_warp_kernel(const LmParams
         // A clean row of Kb elements with hits at positions p_1 < ... < p_h: a miss counts the hits before
         // it, which adds up to h (Kb - 1) - sum p_i - h (h - 1) / 2; spares past the end count nothing.
         int inter = __popc(seen_lo) + __popc(seen_hi);
+        below += below_hi;
         absent_pos >>= ABSENT_SHIFT;
         const int pos_sum = KT * (KT - 1) / 2 - static_cast<int>(absent_pos);
         int serp = inter * Kn - pos_sum;
