@@ -1,16 +1,18 @@
 // List similarity of every (user, variant) list against the user's neutral list:
 // Jaccard (src/utils.py:224-239), SERP* and PRAG* (oracle/np_oracle.py:list_metrics).
 //
-// Table kernel (the fast path): one thread per (user, variant) pair, one CTA per tile of T
-// users.  A tile's lists, lengths and neutral lists are contiguous in HBM and are staged
-// with one-dimensional bulk TMA copies (cp.async.bulk + mbarrier).  Per user slot a
-// `vocab`-entry byte table maps item id -> rank in the neutral list (0xFF = absent);
-// per thread a private `vocab`-bit set (word-interleaved across threads, so every access is
-// bank-conflict free) collapses duplicates exactly as the reference's set() does.  PRAG*'s
-// pair count is a running 64-bit mask of neutral ranks already seen: one __popcll per item.
-//
-// Compare kernel: vocabulary-independent O(K^2) fallback for shapes the table kernel does
-// not cover (V = 1 pair lists of the string API, huge vocabularies, K > 64 Jaccard-only).
+// Four kernels share two data structures -- per user a `vocab`-entry byte table that maps item id ->
+// rank in the neutral list, per (user, variant) row a private `vocab`-bit set that collapses repeated
+// ids exactly as the reference's set() does; PRAG*'s pair count is a running 64-bit mask of the neutral
+// ranks already seen:
+//   warp kernel     17 <= V <= 32, K <= 62 (the benchmark shapes): one warp per user, one lane per variant,
+//                   no block barrier, an optimistic test-and-set main loop with an exact warp-cooperative
+//                   redo of the rare rows that hold a repeat or a foreign id (described at its definition);
+//   register kernel other V up to 128, K <= 62: one thread per pair, one CTA per tile of users, rows in
+//                   registers, tiles staged by bulk TMA copies one tile ahead;
+//   table kernel    K = 63, 64: the same tile structure with the row read from shared memory;
+//   compare kernel  everything else (V = 1 pair lists of the string API, vocabularies beyond 16384 ids,
+//                   K > 64 Jaccard-only): vocabulary-independent O(K^2) compares straight from global memory.
 #include <algorithm>
 #include <cstdlib>
 #include <mutex>
