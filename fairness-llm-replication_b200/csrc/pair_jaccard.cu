@@ -25,7 +25,7 @@ constexpr int PJ_THREADS = 256;
 template <typename StageT>
 __global__ void __launch_bounds__(PJ_THREADS) pair_jaccard_kernel(const int32_t *__restrict__ lists,
                                                                   const int32_t *__restrict__ lens, int64_t U, int M,
-                                                                  int K, int vocab, int Wmax,
+                                                                  int K, int vocab, int Wmax, bool ids_staged,
                                                                   int32_t *__restrict__ out_inter,
                                                                   int32_t *__restrict__ out_sizes) {
     extern __shared__ __align__(16) unsigned int s_mem[];
@@ -34,6 +34,11 @@ __global__ void __launch_bounds__(PJ_THREADS) pair_jaccard_kernel(const int32_t 
     unsigned int *s_bits = s_tab + ((vocab + 3) & ~3);                      // [M][Wp], Wp odd
     const int Wp_max = Wmax | 1;
     StageT *s_inter = reinterpret_cast<StageT *>(s_bits + ((M * Wp_max + 3) & ~3));   // [M][M]
+    // [M * K] the user's ids, read from global memory once per user; 0xFFFF = nothing here (past the row's
+    // length, or outside the vocabulary).  Present only when vocab < 0xFFFF (ids_staged).
+    unsigned short *s_ids = reinterpret_cast<unsigned short *>(
+        reinterpret_cast<unsigned char *>(s_inter) + ((static_cast<size_t>(M) * M * sizeof(StageT) + 15) & ~static_cast<size_t>(15)));
+    constexpr unsigned NONE = 0xFFFFu;
     __shared__ unsigned int s_count;
     const int t = threadIdx.x;
     const int Mh = (M + 1) >> 1;                                // 2x2 blocks per side
@@ -47,28 +52,37 @@ __global__ void __launch_bounds__(PJ_THREADS) pair_jaccard_kernel(const int32_t 
     for (int64_t u = blockIdx.x; u < U; u += gridDim.x) {
         const int32_t *L = lists + u * M * K;
         const int32_t *ln = lens + u * M;
+        if (ids_staged) {
+            // the three passes below walk the user's ids; from global memory each was a chain of dependent
+            // loads (ncu: 45 % of the kernel waiting on them) -- one coalesced sweep into shared memory instead
+            for (int i = t; i < M * K; i += PJ_THREADS) {
+                const int m = i / K, j = i - m * K;
+                const unsigned id = static_cast<unsigned>(L[i]);
+                s_ids[i] = static_cast<unsigned short>((j < min(max(ln[m], 0), K) && id < static_cast<unsigned>(vocab)) ? id : NONE);
+            }
+            __syncthreads();
+        }
+        auto item = [&](int i) -> unsigned {          // id at flat position i of this user, NONE if there is none
+            if (ids_staged) return s_ids[i];
+            const int m = i / K, j = i - m * K;
+            const unsigned id = static_cast<unsigned>(L[i]);
+            return (j < min(max(ln[m], 0), K) && id < static_cast<unsigned>(vocab)) ? id : ~0u;
+        };
         // pass 1: the first thread to touch an item claims it and takes the next local index
         for (int i = t; i < M * K; i += PJ_THREADS) {
-            const int m = i / K, j = i - m * K;
-            if (j < min(max(ln[m], 0), K)) {
-                const unsigned id = static_cast<unsigned>(L[i]);
-                if (id < static_cast<unsigned>(vocab) && s_tab[id] == EMPTY &&
-                    atomicCAS(&s_tab[id], EMPTY, PENDING) == EMPTY)
-                    s_tab[id] = atomicAdd(&s_count, 1u);
-            }
+            const unsigned id = item(i);
+            if (id < static_cast<unsigned>(vocab) && s_tab[id] == EMPTY && atomicCAS(&s_tab[id], EMPTY, PENDING) == EMPTY)
+                s_tab[id] = atomicAdd(&s_count, 1u);
         }
         __syncthreads();
         const int W = static_cast<int>((s_count + 31u) >> 5);             // words actually used (<= Wmax)
         const int Wp = W | 1;                                              // odd stride: a warp's rows hit 32 banks
         // pass 2: set bits in the dense universe
         for (int i = t; i < M * K; i += PJ_THREADS) {
-            const int m = i / K, j = i - m * K;
-            if (j < min(max(ln[m], 0), K)) {
-                const unsigned id = static_cast<unsigned>(L[i]);
-                if (id < static_cast<unsigned>(vocab)) {
-                    const unsigned l = s_tab[id];
-                    atomicOr(&s_bits[m * Wp + (l >> 5)], 1u << (l & 31u));
-                }
+            const unsigned id = item(i);
+            if (id < static_cast<unsigned>(vocab)) {
+                const unsigned l = s_tab[id];
+                atomicOr(&s_bits[(i / K) * Wp + (l >> 5)], 1u << (l & 31u));
             }
         }
         __syncthreads();
@@ -104,9 +118,8 @@ __global__ void __launch_bounds__(PJ_THREADS) pair_jaccard_kernel(const int32_t 
             for (int m = t; m < M; m += PJ_THREADS) out_sizes[u * M + m] = static_cast<int32_t>(s_inter[m * M + m]);
         // restore: forget this user's items, wipe the words that were used
         for (int i = t; i < M * K; i += PJ_THREADS) {
-            const unsigned id = static_cast<unsigned>(L[i]);
-            const int m = i / K, j = i - m * K;
-            if (j < min(max(ln[m], 0), K) && id < static_cast<unsigned>(vocab)) s_tab[id] = EMPTY;
+            const unsigned id = item(i);
+            if (id < static_cast<unsigned>(vocab)) s_tab[id] = EMPTY;
         }
         for (int i = t; i < M * Wp; i += PJ_THREADS) s_bits[i] = 0u;
         if (t == 0) s_count = 0u;
@@ -124,8 +137,10 @@ extern "C" int flr_pair_jaccard(const int32_t *lists, const int32_t *lens, int64
     // a user's M lists hold at most M*K distinct items: that bounds the dense universe
     const int Wmax = static_cast<int>((std::min<int64_t>(static_cast<int64_t>(M) * K, vocab) + 31) / 32);
     const size_t stage_elem = K <= 255 ? 1 : K <= 65535 ? 2 : 4;
+    const bool ids_staged = vocab < 0xFFFF;
     const size_t smem = (static_cast<size_t>((vocab + 3) & ~3) + static_cast<size_t>((M * (Wmax | 1) + 3) & ~3)) * 4 +
-                        ((static_cast<size_t>(M) * M * stage_elem + 15) & ~static_cast<size_t>(15));
+                        ((static_cast<size_t>(M) * M * stage_elem + 15) & ~static_cast<size_t>(15)) +
+                        (ids_staged ? ((static_cast<size_t>(M) * K * 2 + 15) & ~static_cast<size_t>(15)) : 0);
     FLR_REQUIRE(smem <= 226 * 1024, FLR_E_UNSUPPORTED,
                 "pair_jaccard: M=%d lists of up to %d items over %d ids need %zu B of shared memory (max 231424)", M, K,
                 vocab, smem);
@@ -134,8 +149,8 @@ extern "C" int flr_pair_jaccard(const int32_t *lists, const int32_t *lens, int64
     FLR_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
     const int per_sm = std::max<int>(1, static_cast<int>((226 * 1024) / (smem + 1024)));
     const int grid = static_cast<int>(std::min<int64_t>(U, static_cast<int64_t>(device_sm_count()) * per_sm));
-    kern<<<grid, PJ_THREADS, smem, static_cast<cudaStream_t>(stream_)>>>(lists, lens, U, M, K, vocab, Wmax, out_inter,
-                                                                         out_sizes);
+    kern<<<grid, PJ_THREADS, smem, static_cast<cudaStream_t>(stream_)>>>(lists, lens, U, M, K, vocab, Wmax, ids_staged,
+                                                                         out_inter, out_sizes);
     FLR_LAUNCH_CHECK("pair_jaccard_kernel");
     return FLR_OK;
 }
