@@ -579,12 +579,19 @@ struct WkSmem {
     size_t off_recip, warp0, off_stage, off_tab, off_bits, off_row, warp_bytes, total;
 };
 
+// Words between two rows of a staged user block.  Lane l reads row l, so the stride decides the bank
+// conflicts of the row copy: 64-bit loads are conflict-free for K = 2 (mod 4) (half a warp covers 32 banks),
+// 128-bit loads for a stride of 4 (mod 8) (a quarter warp does); K = 0 (mod 8) -- K = 32, 64: every lane on
+// the same banks -- gets four words of padding per row and is copied row by row (from K = 32 up: below that a
+// row is under 128 bytes, too small a bulk copy to be worth it, and the conflicts are 2- to 4-way only).
+__host__ __device__ inline int wk_row_stride(int K) { return (K % 8 == 0 && K >= 32) ? K + 4 : K; }
+
 __host__ __device__ inline WkSmem wk_layout(int V, int K, int KT, int vocab) {
     WkSmem s;
     s.off_recip = 0;
     s.warp0 = align16((2 * KT + 1) * sizeof(double));
     size_t o = 16;                                                    // mbarrier
-    s.off_stage = o; o = align16(o + static_cast<size_t>(V) * K * 4 + 16);     // + 16: the copy starts at a 16-byte boundary
+    s.off_stage = o; o = align16(o + static_cast<size_t>(V) * wk_row_stride(K) * 4 + 16);   // + 16: the copy starts at a 16-byte boundary
     s.off_tab = o;   o = align16(o + static_cast<size_t>(vocab) + 63);          // ids up to vocab + 62 are looked up
     s.off_bits = o;  o = align16(o + (static_cast<size_t>(vocab >> 5) + 3) * 128);
     s.off_row = o;   o = align16(o + static_cast<size_t>(KT) * 4);
@@ -602,7 +609,7 @@ __global__ void __launch_bounds__(NT, 2) list_metrics_warp_kernel(const LmParams
     constexpr bool NARROW = KT <= 32;
     constexpr unsigned TOP = NARROW ? 31u : 63u, ABSENT = TOP + 1u, ABSENT_SHIFT = NARROW ? 5u : 6u;
     constexpr int ABSENT4 = static_cast<int>(ABSENT * 0x01010101u);
-    static_assert(KT % 2 == 0 && KT <= 62, "row length must be even; t = 63 - rank must stay >= 1");
+    static_assert(KT % 2 == 0 && KT <= 64, "row length must be even; ranks must fit the 64-bit mask");
     const int K = p.K, V = p.V, Kn = p.k_cap;
     const unsigned vocab = static_cast<unsigned>(p.vocab);
     const WkSmem L = wk_layout(V, K, KT, p.vocab);
@@ -634,20 +641,35 @@ __global__ void __launch_bounds__(NT, 2) list_metrics_warp_kernel(const LmParams
     __syncthreads();          // the only block-wide barrier: the reciprocal table is shared
 
     const int64_t n_warps = static_cast<int64_t>(gridDim.x) * WK_WARPS;
+    const bool live = lane < V;
+    const int rs = wk_row_stride(K);                     // words between staged rows
+    const bool padded = rs != K, vec4 = (K & 3) == 0;    // padded rows are copied one by one, each by its lane
     const int64_t user_bytes = static_cast<int64_t>(K) * 4 * V, total_bytes = user_bytes * p.U;
     const char *lists_b = reinterpret_cast<const char *>(p.lists);
     // bulk copy of user u's block: from the 16-byte boundary at or below it, a multiple of 16 bytes
     auto bulk_ok = [&](int64_t uu) {
         if (!p.use_bulk || uu >= p.U) return false;
+        if (padded) return true;                 // K % 8 == 0: every row starts and ends on a 16-byte boundary
         const int64_t off = uu * user_bytes, a = off & ~15LL;
         return a + ((off - a + user_bytes + 15) & ~15LL) <= total_bytes;
     };
-    auto issue_tma = [&](int64_t uu) {          // lane 0; the stage buffer must be free
-        const int64_t off = uu * user_bytes, a = off & ~15LL;
-        const uint32_t bytes = static_cast<uint32_t>((off - a + user_bytes + 15) & ~15LL);
-        fence_proxy_async();
-        mbar_expect_tx(bar, bytes);
-        bulk_g2s(s_stage, lists_b + a, bytes, bar);
+    auto issue_tma = [&](int64_t uu) {          // whole warp; the stage buffer must be free
+        const int64_t off = uu * user_bytes;
+        if (padded) {
+            if (lane == 0) {
+                fence_proxy_async();
+                mbar_expect_tx(bar, static_cast<uint32_t>(user_bytes));
+            }
+            __syncwarp();
+            if (live) bulk_g2s(s_stage + static_cast<size_t>(lane) * rs * 4, lists_b + off + static_cast<int64_t>(lane) * K * 4,
+                               static_cast<uint32_t>(K) * 4u, bar);
+        } else if (lane == 0) {
+            const int64_t a = off & ~15LL;
+            const uint32_t bytes = static_cast<uint32_t>((off - a + user_bytes + 15) & ~15LL);
+            fence_proxy_async();
+            mbar_expect_tx(bar, bytes);
+            bulk_g2s(s_stage, lists_b + a, bytes, bar);
+        }
     };
 
     const float inv_serp = 1.0f / static_cast<float>(Kn * (Kn + 1) / 2), inv_prag = 1.0f / static_cast<float>(Kn * (Kn + 1));
@@ -655,7 +677,6 @@ __global__ void __launch_bounds__(NT, 2) list_metrics_warp_kernel(const LmParams
     double acc_j = 0.0;
     long long acc_s = 0, acc_p = 0;
     int acc_n = 0, oov = 0;
-    const bool live = lane < V;
 
     int64_t u = static_cast<int64_t>(blockIdx.x) * WK_WARPS + warp;
     // The small per-user inputs travel in registers, fetched one user ahead -- after the last use of the
@@ -673,7 +694,7 @@ __global__ void __launch_bounds__(NT, 2) list_metrics_warp_kernel(const LmParams
     };
     fetch_small(u, nid0, nid1, nlen, blen);
     bool bulk_cur = bulk_ok(u);
-    if (lane == 0 && bulk_cur) issue_tma(u);
+    if (bulk_cur) issue_tma(u);
 
     for (; u < p.U; u += n_warps) {
         const int64_t un = u + n_warps;
@@ -687,14 +708,24 @@ __global__ void __launch_bounds__(NT, 2) list_metrics_warp_kernel(const LmParams
             phase ^= 1u;
         } else {
             const int32_t *gl = p.lists + u * V * K;
-            for (int i = lane; i < V * K; i += 32) reinterpret_cast<int32_t *>(s_stage)[i] = gl[i];
+            for (int i = lane; i < V * K; i += 32) reinterpret_cast<int32_t *>(s_stage)[(i / K) * rs + i % K] = gl[i];
             __syncwarp();
         }
         unsigned ids[KT];
         const int Kb = live ? max(0, min(blen, Kn)) : K;       // an idle lane redoes lane 0's row; nothing of it is kept
         {
-            const int32_t *row = reinterpret_cast<const int32_t *>(s_stage + delta) + (live ? lane : 0) * K;
-            if (K == KT) {
+            const int32_t *row = reinterpret_cast<const int32_t *>(s_stage + delta) + (live ? lane : 0) * rs;
+            if (vec4) {                              // K % 4 == 0: rows are 16-byte aligned, whole 128-bit chunks
+#pragma unroll
+                for (int j0 = 0; j0 < KT; j0 += 4) {
+                    int4 q = make_int4(0, 0, 0, 0);
+                    if (j0 < K) q = *reinterpret_cast<const int4 *>(row + j0);
+                    const int qq[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+                    for (int e = 0; e < 4; ++e)
+                        if (j0 + e < KT) ids[j0 + e] = j0 < K ? min(static_cast<unsigned>(qq[e]), vocab) : vocab + 1u + j0 + e;
+                }
+            } else if (K == KT) {
 #pragma unroll
                 for (int j0 = 0; j0 < KT; j0 += 2) {
                     const int2 q = *reinterpret_cast<const int2 *>(row + j0);
@@ -714,7 +745,7 @@ __global__ void __launch_bounds__(NT, 2) list_metrics_warp_kernel(const LmParams
                 if (j >= Kb) ids[j] = spare0 + j;
         }
         __syncwarp();
-        if (lane == 0 && bulk_next) issue_tma(un);      // overlaps everything below
+        if (bulk_next) issue_tma(un);                   // overlaps everything below
 
         // ---- rank table: tab[id] = 63 - (first position of id in the neutral list), 64 = absent ----
         int n_a;
@@ -1054,19 +1085,20 @@ Plan make_plan(int64_t U, int V, int K, int k_cap, int vocab) {
     pl.W = (vocab + 31) / 32;
     pl.table = false;
     if (vocab > 0 && vocab <= 16384 && k_cap <= FLR_MAX_RANK_K && V >= 2 && V <= NT) {
-        const int cap = K <= 10 ? 10 : K <= 20 ? 20 : K <= 32 ? 32 : K <= 50 ? 50 : K <= 62 ? 62 : 0;   // unroll capacity
+        const int cap = K <= 10 ? 10 : K <= 20 ? 20 : K <= 32 ? 32 : K <= 50 ? 50 : K <= 62 ? 62 : 0;   // unroll capacity (register kernel)
+        const int wcap = K > 64 ? 0 : K > 50 ? 64 : cap;                                                 // ... of the warp kernel: K <= 64
         const bool reg = cap != 0;
         const char *pick = getenv("FLR_LM_KERNEL");
         // the warp kernel's four per-warp regions must fit one SM (vocabularies up to ~9000 ids do; with more
         // than half of it only one CTA is resident per SM); larger vocabularies fall through to the tile
         // kernels and from there to the compare kernel
-        if (reg && V >= 17 && V <= 32 && !(pick && pick[0] == 'r') &&
-            wk_layout(V, K, cap, vocab).total <= static_cast<size_t>(226 * 1024)) {
+        if (wcap != 0 && V >= 17 && V <= 32 && !(pick && pick[0] == 'r') &&
+            wk_layout(V, K, wcap, vocab).total <= static_cast<size_t>(226 * 1024)) {
             pl.table = true;
             pl.warp = true;
-            pl.reg_k = cap;
+            pl.reg_k = wcap;
             pl.T = WK_WARPS;
-            pl.smem = wk_layout(V, K, cap, vocab).total;
+            pl.smem = wk_layout(V, K, wcap, vocab).total;
             const int64_t tiles = (U + WK_WARPS - 1) / WK_WARPS;
             pl.grid = static_cast<int>(std::min<int64_t>(std::max<int64_t>(tiles, 1), 2LL * sms));
             return pl;
@@ -1114,7 +1146,7 @@ TableKernel pick_table_kernel(const Plan &pl, int K, bool rank) {
             case 20: return rank ? list_metrics_warp_kernel<20, true> : list_metrics_warp_kernel<20, false>;
             case 32: return rank ? list_metrics_warp_kernel<32, true> : list_metrics_warp_kernel<32, false>;
             case 50: return rank ? list_metrics_warp_kernel<50, true> : list_metrics_warp_kernel<50, false>;
-            case 62: return rank ? list_metrics_warp_kernel<62, true> : list_metrics_warp_kernel<62, false>;
+            case 64: return rank ? list_metrics_warp_kernel<64, true> : list_metrics_warp_kernel<64, false>;
             default: break;
         }
     }

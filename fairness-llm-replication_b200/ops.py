@@ -136,9 +136,10 @@ def list_metrics_kernel_name(V: int, K: int, vocab: int, k_cap: Optional[int] = 
     r = 1 if rank_metrics else 0
     if 0 < vocab <= 16384 and k_cap <= MAX_RANK_K and 2 <= V <= 128:
         cap = next((c for c in (10, 20, 32, 50, 62) if K <= c), 0)
-        warp_bytes = 16 + ((V * K * 4 + 16 + 15) & ~15) + ((vocab + 63 + 15) & ~15) + ((vocab >> 5) + 3) * 128 + ((cap * 4 + 15) & ~15)
-        if cap and 17 <= V <= 32 and 4 * warp_bytes + (2 * cap + 1) * 8 + 16 <= 226 * 1024:
-            return "list_metrics_warp_kernel<%d,%d>" % (cap, r)
+        wcap = 0 if K > 64 else 64 if K > 50 else cap
+        warp_bytes = 16 + ((V * K * 4 + 16 + 15) & ~15) + ((vocab + 63 + 15) & ~15) + ((vocab >> 5) + 3) * 128 + ((wcap * 4 + 15) & ~15)
+        if wcap and 17 <= V <= 32 and 4 * warp_bytes + (2 * wcap + 1) * 8 + 16 <= 226 * 1024:
+            return "list_metrics_warp_kernel<%d,%d>" % (wcap, r)
         if cap:
             return "list_metrics_reg_kernel<%d,%d>" % (cap, r)
         return "list_metrics_table_kernel<%d,%d>" % (4 if K % 4 == 0 else 2 if K % 2 == 0 else 1, r)

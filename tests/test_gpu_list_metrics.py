@@ -65,7 +65,7 @@ def test_table_kernel_random(V, K):
         _check(*case, vocab=vocab, k_cap=K // 2)
 
 
-@pytest.mark.parametrize("V,K,vocab", [(17, 33, 3706), (24, 62, 3706), (29, 50, 200), (31, 32, 64), (20, 11, 5000), (31, 20, 8000), (32, 45, 16384)])
+@pytest.mark.parametrize("V,K,vocab", [(17, 33, 3706), (24, 62, 3706), (31, 64, 3706), (19, 63, 300), (29, 50, 200), (31, 32, 64), (20, 11, 5000), (31, 20, 8000), (32, 45, 16384)])
 def test_warp_kernel_shapes(V, K, vocab):
     """The warp kernel's corners: idle lanes (V < 32), rows longer than one 32-wide half (K > 32), rows below
     the unroll capacity (K between capacities), tiny vocabularies (nearly every row has a repeat and goes
