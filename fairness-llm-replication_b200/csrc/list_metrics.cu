@@ -490,16 +490,14 @@ __global__ void __launch_bounds__(NT, 2) list_metrics_reg_kernel(const LmParams 
         }
         __syncthreads();
 
-        // ---- wipe every private bit set with 128-bit stores, re-arm the spare element's word (each
-        //      thread its own: the sweep stops short of that row), and un-mark the rank tables ----
-        {
-            int4 *bits4 = reinterpret_cast<int4 *>(s_bits);
-            const int spare_row = static_cast<int>(vocab >> 5);
-            const int n4 = spare_row * (NT / 4);
-            const int4 zero = make_int4(0, 0, 0, 0);
-#pragma unroll 8
-            for (int i = t; i < n4; i += NT) bits4[i] = zero;
-            s_bits[spare_row * NT + t] = 1u << (vocab & 31u);
+        // ---- un-set the bits this thread set (every one lives in the word of one of its ids: K word stores
+        //      instead of a sweep over all the bit sets), re-arm the spare element, un-mark the rank tables ----
+        if (live) {
+            char *bits_base = reinterpret_cast<char *>(s_bits + t);
+#pragma unroll
+            for (int j = 0; j < KT; ++j)
+                *reinterpret_cast<uint32_t *>(bits_base + (min(ids[j], vocab) >> 5) * (NT * 4)) = 0u;
+            s_bits[(vocab >> 5) * NT + t] = 1u << (vocab & 31u);
         }
         for (int s = warp; s < tu; s += NT / 32) {
             const int32_t *A = s_keep + s * KT;
@@ -510,8 +508,8 @@ __global__ void __launch_bounds__(NT, 2) list_metrics_reg_kernel(const LmParams 
             }
             __syncwarp();      // every lane's un-mark lands before any lane of this warp re-marks the table
         }
-        // no barrier here: the next tile's first barrier orders this wipe before its main loop, and
-        // each table is rebuilt by the warp that just un-marked it
+        // no barrier here: a thread's bit set is its own, and each table is rebuilt by the warp that just
+        // un-marked it
     }
 
     double *dst = p.partial + (static_cast<size_t>(blockIdx.x) * NT + t) * 4;
