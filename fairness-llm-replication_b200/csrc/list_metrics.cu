@@ -1090,8 +1090,7 @@ Plan make_plan(int64_t U, int V, int K, int k_cap, int vocab) {
         // the warp kernel's four per-warp regions must fit one SM (vocabularies up to ~9000 ids do; with more
         // than half of it only one CTA is resident per SM); larger vocabularies fall through to the tile
         // kernels and from there to the compare kernel
-        if (wcap != 0 && V >= 17 && V <= 32 && !(pick && pick[0] == 'r') &&
-            wk_layout(V, K, wcap, vocab).total <= static_cast<size_t>(226 * 1024)) {
+        auto plan_warp = [&]() {
             pl.table = true;
             pl.warp = true;
             pl.reg_k = wcap;
@@ -1099,6 +1098,11 @@ Plan make_plan(int64_t U, int V, int K, int k_cap, int vocab) {
             pl.smem = wk_layout(V, K, wcap, vocab).total;
             const int64_t tiles = (U + WK_WARPS - 1) / WK_WARPS;
             pl.grid = static_cast<int>(std::min<int64_t>(std::max<int64_t>(tiles, 1), 2LL * sms));
+        };
+        const bool warp_fits = wcap != 0 && V <= 32 && !(pick && pick[0] == 'r') &&
+                               wk_layout(V, K, wcap, vocab).total <= static_cast<size_t>(226 * 1024);
+        if (warp_fits && V >= 17) {
+            plan_warp();
             return pl;
         }
         // register kernel extras: neutral ids + lengths of the live tile, and the reciprocal table
@@ -1117,6 +1121,10 @@ Plan make_plan(int64_t U, int V, int K, int k_cap, int vocab) {
             pl.smem = bytes(T);
             const int64_t tiles = (U + T - 1) / T;
             pl.grid = static_cast<int>(std::min<int64_t>(std::max<int64_t>(tiles, 1), 2LL * sms));
+        } else if (warp_fits) {
+            // few variants with long rows: no tile of users fits the tile kernels' shared memory; a warp per
+            // user with V of its 32 lanes busy is still far ahead of the O(K^2) compare kernel
+            plan_warp();
         }
     }
     if (!pl.table) {

@@ -130,19 +130,38 @@ def list_metrics_counts(neutral, neutral_len, lists, lens, *, vocab: int, k_cap:
 
 
 def list_metrics_kernel_name(V: int, K: int, vocab: int, k_cap: Optional[int] = None, rank_metrics: bool = True) -> str:
-    """Name of the kernel ``list_metrics`` launches for a shape (the plan of csrc/list_metrics.cu:make_plan),
+    """Name of the kernel ``list_metrics`` launches for a shape (mirrors csrc/list_metrics.cu:make_plan),
     for labelling measurements: what ncu and the profiler list is this name."""
     k_cap = K if k_cap is None else min(k_cap, K)
     r = 1 if rank_metrics else 0
+    a16 = lambda x: (x + 15) & ~15
     if 0 < vocab <= 16384 and k_cap <= MAX_RANK_K and 2 <= V <= 128:
         cap = next((c for c in (10, 20, 32, 50, 62) if K <= c), 0)
         wcap = 0 if K > 64 else 64 if K > 50 else cap
-        warp_bytes = 16 + ((V * K * 4 + 16 + 15) & ~15) + ((vocab + 63 + 15) & ~15) + ((vocab >> 5) + 3) * 128 + ((wcap * 4 + 15) & ~15)
-        if wcap and 17 <= V <= 32 and 4 * warp_bytes + (2 * wcap + 1) * 8 + 16 <= 226 * 1024:
-            return "list_metrics_warp_kernel<%d,%d>" % (wcap, r)
-        if cap:
-            return "list_metrics_reg_kernel<%d,%d>" % (cap, r)
-        return "list_metrics_table_kernel<%d,%d>" % (4 if K % 4 == 0 else 2 if K % 2 == 0 else 1, r)
+        rs = K + 4 if (K % 8 == 0 and K >= 32) else K
+        warp_bytes = 16 + a16(V * rs * 4 + 16) + a16(vocab + 63) + a16(((vocab >> 5) + 3) * 128) + a16(wcap * 4)
+        warp_fits = bool(wcap) and V <= 32 and a16((2 * wcap + 1) * 8) + 4 * ((warp_bytes + 127) & ~127) <= 226 * 1024
+        warp_name = "list_metrics_warp_kernel<%d,%d>" % (wcap, r)
+        if warp_fits and V >= 17:
+            return warp_name
+        vocab_pad, W = (vocab + 16) & ~15, (vocab + 31) // 32
+
+        def tile_bytes(T):
+            n = 16
+            for part in (T * V * K * 4, T * K * 4, T * V * 4, T * 4, T * 4, T * vocab_pad, (W + 1) * 128 * 4):
+                n = a16(n + part)
+            return n + (a16(T * (cap * 4 + 4)) + a16((2 * cap + 1) * 8) if cap else 0)
+        T = 128 // V
+        if T >= 4:
+            T &= ~3
+        while T >= 1 and tile_bytes(T) > 110 * 1024:
+            T = ((T - 1) & ~3) if T > 4 else T - 1
+        if T >= 1 and T * V * 2 >= 128:
+            if cap:
+                return "list_metrics_reg_kernel<%d,%d>" % (cap, r)
+            return "list_metrics_table_kernel<%d,%d>" % (4 if K % 4 == 0 else 2 if K % 2 == 0 else 1, r)
+        if warp_fits:
+            return warp_name
     return "list_metrics_cmp_kernel<%d>" % r
 
 
