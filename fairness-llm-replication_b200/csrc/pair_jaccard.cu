@@ -4,8 +4,8 @@
 // One CTA per user: the M ranked lists become M item bit sets in shared memory (row stride padded to
 // an odd word count so a warp's 32 rows hit 32 banks), every pair's intersection is a __popc sum over
 // AND-ed words, and the M x M matrix is assembled in shared memory so the global store is one
-// coalesced sweep.  Each thread owns a 2 x 2 block of pairs so every word loaded from shared memory
-// feeds two ANDs.
+// coalesced sweep.  Each thread owns a 4 x 4 block of pairs so every word loaded from shared memory
+// feeds four ANDs.
 #include <algorithm>
 
 #include "common.cuh"
@@ -41,7 +41,8 @@ __global__ void __launch_bounds__(PJ_THREADS) pair_jaccard_kernel(const int32_t 
     constexpr unsigned NONE = 0xFFFFu;
     __shared__ unsigned int s_count;
     const int t = threadIdx.x;
-    const int Mh = (M + 1) >> 1;                                // 2x2 blocks per side
+    constexpr int PB = 4;                                       // a thread owns a PB x PB block of pairs
+    const int Mh = (M + PB - 1) / PB;                           // blocks per side
     const int n_blocks = Mh * (Mh + 1) / 2;                     // blocks (bm, bn) with bn >= bm
 
     for (int i = t; i < vocab; i += PJ_THREADS) s_tab[i] = EMPTY;
@@ -94,22 +95,37 @@ __global__ void __launch_bounds__(PJ_THREADS) pair_jaccard_kernel(const int32_t 
             while (bm > 0 && bm * Mh - bm * (bm - 1) / 2 > blk) --bm;
             while ((bm + 1) * Mh - (bm + 1) * bm / 2 <= blk) ++bm;
             const int bn = bm + (blk - (bm * Mh - bm * (bm - 1) / 2));
-            // a block pairs rows {bm, bm+Mh} with {bn, bn+Mh}: lanes read consecutive rows (stride Wp, odd)
-            const int m0 = bm, m1 = min(bm + Mh, M - 1), n0 = bn, n1 = min(bn + Mh, M - 1);
-            const unsigned int *a0 = s_bits + m0 * Wp, *a1 = s_bits + m1 * Wp;
-            const unsigned int *b0 = s_bits + n0 * Wp, *b1 = s_bits + n1 * Wp;
-            int c00 = 0, c01 = 0, c10 = 0, c11 = 0;
-            for (int w = 0; w < W; ++w) {
-                const unsigned int x0 = a0[w], x1 = a1[w], y0 = b0[w], y1 = b1[w];
-                c00 += __popc(x0 & y0); c01 += __popc(x0 & y1);
-                c10 += __popc(x1 & y0); c11 += __popc(x1 & y1);
+            // a block pairs rows {bm + i Mh} with rows {bn + j Mh}, i, j < PB (clipped to M - 1: a clipped row
+            // repeats a value that is written anyway); lanes read consecutive rows (stride Wp, odd).  Every
+            // word loaded from shared memory feeds PB ANDs: the loop is bound by those loads.
+            const unsigned int *ar[PB], *br[PB];
+            int mi[PB], nj[PB], c[PB][PB];
+#pragma unroll
+            for (int i = 0; i < PB; ++i) {
+                mi[i] = min(bm + i * Mh, M - 1);
+                nj[i] = min(bn + i * Mh, M - 1);
+                ar[i] = s_bits + mi[i] * Wp;
+                br[i] = s_bits + nj[i] * Wp;
+#pragma unroll
+                for (int j = 0; j < PB; ++j) c[i][j] = 0;
             }
-            const StageT v00 = static_cast<StageT>(c00), v01 = static_cast<StageT>(c01);
-            const StageT v10 = static_cast<StageT>(c10), v11 = static_cast<StageT>(c11);
-            s_inter[m0 * M + n0] = v00; s_inter[n0 * M + m0] = v00;
-            s_inter[m0 * M + n1] = v01; s_inter[n1 * M + m0] = v01;
-            s_inter[m1 * M + n0] = v10; s_inter[n0 * M + m1] = v10;
-            s_inter[m1 * M + n1] = v11; s_inter[n1 * M + m1] = v11;
+            for (int w = 0; w < W; ++w) {
+                unsigned int x[PB], y[PB];
+#pragma unroll
+                for (int i = 0; i < PB; ++i) { x[i] = ar[i][w]; y[i] = br[i][w]; }
+#pragma unroll
+                for (int i = 0; i < PB; ++i)
+#pragma unroll
+                    for (int j = 0; j < PB; ++j) c[i][j] += __popc(x[i] & y[j]);
+            }
+#pragma unroll
+            for (int i = 0; i < PB; ++i)
+#pragma unroll
+                for (int j = 0; j < PB; ++j) {
+                    const StageT v = static_cast<StageT>(c[i][j]);
+                    s_inter[mi[i] * M + nj[j]] = v;
+                    s_inter[nj[j] * M + mi[i]] = v;
+                }
         }
         __syncthreads();
         int32_t *dst = out_inter + u * M * M;
