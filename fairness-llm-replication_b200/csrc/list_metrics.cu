@@ -5,10 +5,11 @@
 // rank in the neutral list, per (user, variant) row a private `vocab`-bit set that collapses repeated
 // ids exactly as the reference's set() does; PRAG*'s pair count is a running 64-bit mask of the neutral
 // ranks already seen:
-//   warp kernel     17 <= V <= 32, K <= 62 (the benchmark shapes): one warp per user, one lane per variant,
+//   warp kernel     17 <= V <= 128, K <= 64 (the benchmark shapes): one warp per user, one lane per variant,
 //                   no block barrier, an optimistic test-and-set main loop with an exact warp-cooperative
 //                   redo of the rare rows that hold a repeat or a foreign id (described at its definition);
-//   register kernel other V up to 128, K <= 62: one thread per pair, one CTA per tile of users, rows in
+//                   more than 32 variants run as one launch per chunk of 32;
+//   register kernel V < 17, K <= 62: one thread per pair, one CTA per tile of users, rows in
 //                   registers, tiles staged by bulk TMA copies one tile ahead;
 //   table kernel    K = 63, 64: the same tile structure with the row read from shared memory;
 //   compare kernel  everything else (V = 1 pair lists of the string API, vocabularies beyond 16384 ids,
@@ -35,6 +36,7 @@ struct LmParams {
     float *out_jac, *out_serp, *out_prag;
     double *partial;
     int32_t *status;
+    int v0, Vt;        // chunked warp kernel only: first variant of this launch's chunk, variants per user in memory
 };
 
 struct LmSmem {
@@ -521,7 +523,7 @@ __global__ void __launch_bounds__(NT, 2) list_metrics_reg_kernel(const LmParams 
 }
 
 // ---------------------------------------------------------------------------------------
-// Warp kernel (the fast path for 17 <= V <= 32, K <= 62): one warp per user, one lane per variant,
+// Warp kernel (the fast path for 17 <= V <= 128, K <= 64; V > 32 in chunks of 32): one warp per user, one lane per variant,
 // and no block-wide barrier anywhere -- every warp of a CTA runs its own pipeline over its own
 // shared-memory region (stage buffer, rank table, bit sets, mbarrier), so while one warp builds a
 // table or writes results another is in its main loop.
@@ -590,7 +592,7 @@ __host__ __device__ inline WkSmem wk_layout(int V, int K, int KT, int vocab) {
     s.warp0 = align16((2 * KT + 1) * sizeof(double));
     size_t o = 16;                                                    // mbarrier
     s.off_stage = o; o = align16(o + static_cast<size_t>(V) * wk_row_stride(K) * 4 + 16);   // + 16: the copy starts at a 16-byte boundary
-    s.off_tab = o;   o = align16(o + static_cast<size_t>(vocab) + 63);          // ids up to vocab + 62 are looked up
+    s.off_tab = o;   o = align16(o + static_cast<size_t>(vocab) + 65);          // ids up to vocab + 64 (the spare of position 63) are looked up
     s.off_bits = o;  o = align16(o + (static_cast<size_t>(vocab >> 5) + 3) * 128);
     s.off_row = o;   o = align16(o + static_cast<size_t>(KT) * 4);
     s.warp_bytes = (o + 127) & ~static_cast<size_t>(127);
@@ -598,7 +600,10 @@ __host__ __device__ inline WkSmem wk_layout(int V, int K, int KT, int vocab) {
     return s;
 }
 
-template <int KT, bool RANK>
+// CHUNKED: users with more than 32 variants are scored in launches of up to 32 variants each -- this launch
+// takes variants [p.v0, p.v0 + p.V) of the p.Vt every user holds.  A compile-time flag, so that the common
+// one-chunk kernels carry none of the extra address arithmetic.
+template <int KT, bool RANK, bool CHUNKED>
 __global__ void __launch_bounds__(NT, 2) list_metrics_warp_kernel(const LmParams p) {
     extern __shared__ __align__(128) unsigned char smem[];
     constexpr unsigned FULL = 0xffffffffu;
@@ -609,6 +614,7 @@ __global__ void __launch_bounds__(NT, 2) list_metrics_warp_kernel(const LmParams
     constexpr int ABSENT4 = static_cast<int>(ABSENT * 0x01010101u);
     static_assert(KT % 2 == 0 && KT <= 64, "row length must be even; ranks must fit the 64-bit mask");
     const int K = p.K, V = p.V, Kn = p.k_cap;
+    const int Vt = CHUNKED ? p.Vt : V, v0 = CHUNKED ? p.v0 : 0;
     const unsigned vocab = static_cast<unsigned>(p.vocab);
     const WkSmem L = wk_layout(V, K, KT, p.vocab);
     const int t = threadIdx.x, lane = t & 31;
@@ -642,17 +648,19 @@ __global__ void __launch_bounds__(NT, 2) list_metrics_warp_kernel(const LmParams
     const bool live = lane < V;
     const int rs = wk_row_stride(K);                     // words between staged rows
     const bool padded = rs != K, vec4 = (K & 3) == 0;    // padded rows are copied one by one, each by its lane
-    const int64_t user_bytes = static_cast<int64_t>(K) * 4 * V, total_bytes = user_bytes * p.U;
-    const char *lists_b = reinterpret_cast<const char *>(p.lists);
+    // user_bytes: what one launch copies per user; a user's rows are user_stride apart in memory
+    const int64_t user_bytes = static_cast<int64_t>(K) * 4 * V, user_stride = static_cast<int64_t>(K) * 4 * Vt;
+    const int64_t total_bytes = user_stride * p.U;
+    const char *lists_b = reinterpret_cast<const char *>(p.lists) + static_cast<int64_t>(v0) * K * 4;
     // bulk copy of user u's block: from the 16-byte boundary at or below it, a multiple of 16 bytes
     auto bulk_ok = [&](int64_t uu) {
         if (!p.use_bulk || uu >= p.U) return false;
         if (padded) return true;                 // K % 8 == 0: every row starts and ends on a 16-byte boundary
-        const int64_t off = uu * user_bytes, a = off & ~15LL;
-        return a + ((off - a + user_bytes + 15) & ~15LL) <= total_bytes;
+        const int64_t off = uu * user_stride, a = off & ~15LL;       // relative to lists_b (itself 16-byte aligned)
+        return a + ((off - a + user_bytes + 15) & ~15LL) <= total_bytes - static_cast<int64_t>(v0) * K * 4;
     };
     auto issue_tma = [&](int64_t uu) {          // whole warp; the stage buffer must be free
-        const int64_t off = uu * user_bytes;
+        const int64_t off = uu * user_stride;
         if (padded) {
             if (lane == 0) {
                 fence_proxy_async();
@@ -687,7 +695,7 @@ __global__ void __launch_bounds__(NT, 2) list_metrics_warp_kernel(const LmParams
             a0 = lane < K ? static_cast<unsigned>(A[lane]) : vocab;
             a1 = lane + 32 < K ? static_cast<unsigned>(A[lane + 32]) : vocab;
             nl = p.neutral_len[uu];
-            bl = live ? p.lens[uu * V + lane] : K;
+            bl = live ? p.lens[uu * Vt + v0 + lane] : K;
         }
     };
     fetch_small(u, nid0, nid1, nlen, blen);
@@ -701,11 +709,11 @@ __global__ void __launch_bounds__(NT, 2) list_metrics_warp_kernel(const LmParams
         // ---- stage -> registers ----
         int delta = 0;
         if (bulk_cur) {
-            delta = static_cast<int>((u * user_bytes) & 15);
+            delta = static_cast<int>((u * user_stride) & 15);
             mbar_wait(bar, phase);
             phase ^= 1u;
         } else {
-            const int32_t *gl = p.lists + u * V * K;
+            const int32_t *gl = p.lists + (u * Vt + v0) * K;
             for (int i = lane; i < V * K; i += 32) reinterpret_cast<int32_t *>(s_stage)[(i / K) * rs + i % K] = gl[i];
             __syncwarp();
         }
@@ -750,7 +758,7 @@ __global__ void __launch_bounds__(NT, 2) list_metrics_warp_kernel(const LmParams
         {
             const int Ka = max(0, min(nlen, Kn));
             const unsigned id0 = lane < Ka ? nid0 : vocab, id1 = lane + 32 < Ka ? nid1 : vocab;
-            oov += (lane < Ka && id0 >= vocab ? 1 : 0) + (lane + 32 < Ka && id1 >= vocab ? 1 : 0);
+            if (v0 == 0) oov += (lane < Ka && id0 >= vocab ? 1 : 0) + (lane + 32 < Ka && id1 >= vocab ? 1 : 0);   // once per user
             const unsigned t0 = TOP - lane, t1 = TOP - 32u - lane;      // t of positions lane and lane + 32 (t1 unused when NARROW)
             if (id1 < vocab) tab[id1] = static_cast<uint8_t>(t1);       // later half first,
             __syncwarp();
@@ -888,7 +896,7 @@ __global__ void __launch_bounds__(NT, 2) list_metrics_warp_kernel(const LmParams
             // quotient, which the fp32 output and the 1e-12 tolerance on the sums never see
             double jac = static_cast<double>(inter) * s_recip[uni];
             if (p.empty_policy == FLR_EMPTY_BOTH_IS_ONE) jac = uni > 0 ? jac : 1.0;
-            const int64_t pair = u * V + lane;
+            const int64_t pair = u * Vt + v0 + lane;
             if (p.out_inter) p.out_inter[pair] = inter;
             if (p.out_union) p.out_union[pair] = uni;
             if (p.out_jac) p.out_jac[pair] = static_cast<float>(jac);
@@ -1071,6 +1079,7 @@ struct Plan {
     bool table;        // table / register / test-and-set kernel (else compare kernel)
     int reg_k;         // unroll capacity of the register kernels (>= K), 0 = generic table kernel (K = 63, 64)
     bool warp;         // warp kernel (one warp per user) instead of the register kernel
+    int chunks;        // warp kernel: launches per call, one per 32 variants
     int T, vocab_pad, W, grid;
     size_t smem;
     int64_t cmp_threads;
@@ -1090,17 +1099,21 @@ Plan make_plan(int64_t U, int V, int K, int k_cap, int vocab) {
         // the warp kernel's four per-warp regions must fit one SM (vocabularies up to ~9000 ids do; with more
         // than half of it only one CTA is resident per SM); larger vocabularies fall through to the tile
         // kernels and from there to the compare kernel
+        const int Vw = std::min(V, 32);          // variants per launch of the warp kernel
         auto plan_warp = [&]() {
             pl.table = true;
             pl.warp = true;
+            pl.chunks = (V + 31) / 32;
             pl.reg_k = wcap;
             pl.T = WK_WARPS;
-            pl.smem = wk_layout(V, K, wcap, vocab).total;
+            pl.smem = wk_layout(Vw, K, wcap, vocab).total;
             const int64_t tiles = (U + WK_WARPS - 1) / WK_WARPS;
             pl.grid = static_cast<int>(std::min<int64_t>(std::max<int64_t>(tiles, 1), 2LL * sms));
         };
-        const bool warp_fits = wcap != 0 && V <= 32 && !(pick && pick[0] == 'r') &&
-                               wk_layout(V, K, wcap, vocab).total <= static_cast<size_t>(226 * 1024);
+        // more than 32 variants: one launch per chunk of 32 (a chunk starts 128 * K bytes into the user's block,
+        // so the bulk copies' alignment arithmetic is that of the one-chunk case)
+        const bool warp_fits = wcap != 0 && !(pick && pick[0] == 'r') &&
+                               wk_layout(Vw, K, wcap, vocab).total <= static_cast<size_t>(226 * 1024);
         if (warp_fits && V >= 17) {
             plan_warp();
             return pl;
@@ -1147,14 +1160,13 @@ using TableKernel = void (*)(const LmParams);
 
 TableKernel pick_table_kernel(const Plan &pl, int K, bool rank) {
     if (pl.warp) {
+#define FLR_WARP_CASE(KT_) case KT_: return pl.chunks > 1 ? (rank ? list_metrics_warp_kernel<KT_, true, true> : list_metrics_warp_kernel<KT_, false, true>) \
+                                                          : (rank ? list_metrics_warp_kernel<KT_, true, false> : list_metrics_warp_kernel<KT_, false, false>);
         switch (pl.reg_k) {
-            case 10: return rank ? list_metrics_warp_kernel<10, true> : list_metrics_warp_kernel<10, false>;
-            case 20: return rank ? list_metrics_warp_kernel<20, true> : list_metrics_warp_kernel<20, false>;
-            case 32: return rank ? list_metrics_warp_kernel<32, true> : list_metrics_warp_kernel<32, false>;
-            case 50: return rank ? list_metrics_warp_kernel<50, true> : list_metrics_warp_kernel<50, false>;
-            case 64: return rank ? list_metrics_warp_kernel<64, true> : list_metrics_warp_kernel<64, false>;
+            FLR_WARP_CASE(10) FLR_WARP_CASE(20) FLR_WARP_CASE(32) FLR_WARP_CASE(50) FLR_WARP_CASE(64)
             default: break;
         }
+#undef FLR_WARP_CASE
     }
     switch (pl.reg_k) {
         case 10: return rank ? list_metrics_reg_kernel<10, true> : list_metrics_reg_kernel<10, false>;
@@ -1194,12 +1206,26 @@ int launch_planned(const Plan &pl, LmParams p, int rank_metrics, double *out_var
                                    aligned16(p.lens);
         TableKernel kern = pick_table_kernel(pl, p.K, rank_metrics != 0);
         FLR_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(pl.smem)));
+        if (pl.warp) {
+            // one launch per chunk of 32 variants (one launch in all for V <= 32); the chunks reuse the partials
+            const int Vt = p.V;
+            for (int c = 0; c < pl.chunks; ++c) {
+                p.Vt = Vt;
+                p.v0 = 32 * c;
+                p.V = std::min(32, Vt - p.v0);
+                kern<<<pl.grid, NT, pl.smem, stream>>>(p);
+                FLR_LAUNCH_CHECK("list_metrics_warp_kernel");
+                if (out_variant_sums) {
+                    list_metrics_warp_finalize_kernel<<<(p.V + 3) / 4, 128, 0, stream>>>(p.partial, pl.grid, p.V,
+                                                                                         out_variant_sums + 4 * p.v0);
+                    FLR_LAUNCH_CHECK("list_metrics_warp_finalize_kernel");
+                }
+            }
+            return FLR_OK;
+        }
         kern<<<pl.grid, NT, pl.smem, stream>>>(p);
         FLR_LAUNCH_CHECK("list_metrics table/register kernel");
-        if (out_variant_sums && pl.warp) {
-            list_metrics_warp_finalize_kernel<<<(p.V + 3) / 4, 128, 0, stream>>>(p.partial, pl.grid, p.V, out_variant_sums);
-            FLR_LAUNCH_CHECK("list_metrics_warp_finalize_kernel");
-        } else if (out_variant_sums) {
+        if (out_variant_sums) {
             list_metrics_finalize_kernel<<<(p.V + 3) / 4, 128, 0, stream>>>(p.partial, pl.grid, NT, pl.T, p.V,
                                                                              out_variant_sums);
             FLR_LAUNCH_CHECK("list_metrics_finalize_kernel");

@@ -139,9 +139,10 @@ def list_metrics_kernel_name(V: int, K: int, vocab: int, k_cap: Optional[int] = 
         cap = next((c for c in (10, 20, 32, 50, 62) if K <= c), 0)
         wcap = 0 if K > 64 else 64 if K > 50 else cap
         rs = K + 4 if (K % 8 == 0 and K >= 32) else K
-        warp_bytes = 16 + a16(V * rs * 4 + 16) + a16(vocab + 63) + a16(((vocab >> 5) + 3) * 128) + a16(wcap * 4)
-        warp_fits = bool(wcap) and V <= 32 and a16((2 * wcap + 1) * 8) + 4 * ((warp_bytes + 127) & ~127) <= 226 * 1024
-        warp_name = "list_metrics_warp_kernel<%d,%d>" % (wcap, r)
+        Vw = min(V, 32)                    # variants per launch; more than 32 go in chunks of 32
+        warp_bytes = 16 + a16(Vw * rs * 4 + 16) + a16(vocab + 65) + a16(((vocab >> 5) + 3) * 128) + a16(wcap * 4)
+        warp_fits = bool(wcap) and a16((2 * wcap + 1) * 8) + 4 * ((warp_bytes + 127) & ~127) <= 226 * 1024
+        warp_name = "list_metrics_warp_kernel<%d,%d,%d>" % (wcap, r, 1 if V > 32 else 0)
         if warp_fits and V >= 17:
             return warp_name
         vocab_pad, W = (vocab + 16) & ~15, (vocab + 31) // 32

@@ -65,15 +65,33 @@ def test_table_kernel_random(V, K):
         _check(*case, vocab=vocab, k_cap=K // 2)
 
 
-@pytest.mark.parametrize("V,K,vocab", [(17, 33, 3706), (24, 62, 3706), (31, 64, 3706), (19, 63, 300), (29, 50, 200), (31, 32, 64), (20, 11, 5000), (31, 20, 8000), (32, 45, 16384)])
+@pytest.mark.parametrize("V,K,vocab", [(17, 33, 3706), (24, 62, 3706), (31, 64, 3706), (19, 63, 300), (29, 50, 200), (31, 32, 64), (20, 11, 5000), (31, 20, 8000), (32, 45, 16384),
+                                       (32, 64, 2000), (31, 56, 2001)])
 def test_warp_kernel_shapes(V, K, vocab):
     """The warp kernel's corners: idle lanes (V < 32), rows longer than one 32-wide half (K > 32), rows below
     the unroll capacity (K between capacities), tiny vocabularies (nearly every row has a repeat and goes
-    through the exact warp-cooperative pass), the largest vocabulary the table kernels take."""
+    through the exact warp-cooperative pass), the largest vocabulary the table kernels take, vocabularies
+    that end on a 16-byte boundary of the rank table (the spare id of position 63 is the last byte looked up)."""
     rng = np.random.default_rng(V * 1000 + K)
     case = _random_case(rng, 131, V, K, min(vocab, 4 * K))
     _check(*case, vocab=vocab)
     _check(*case, vocab=vocab, empty_policy=0, k_cap=max(1, K - 7))
+    _check(*case, vocab=vocab, rank=False)
+
+
+@pytest.mark.parametrize("V,K,vocab", [(33, 20, 3706), (40, 20, 3706), (64, 50, 3706), (65, 7, 500), (97, 33, 3706),
+                                       (124, 20, 3706), (128, 64, 2000), (100, 48, 8000), (45, 19, 90)])
+def test_warp_kernel_chunked_shapes(V, K, vocab):
+    """More than 32 variants per user: the warp kernel runs once per chunk of 32 variants (a last chunk of
+    one variant, odd K and so unaligned chunk rows, padded rows, the widest user the table kernels take).
+    Per-variant sums land in each chunk's own slice; foreign ids of the neutral list count once per user."""
+    from fairness_llm_replication_b200 import ops
+    assert ops.list_metrics_kernel_name(V, K, vocab).startswith("list_metrics_warp_kernel") and \
+        ops.list_metrics_kernel_name(V, K, vocab).endswith(",1>")
+    rng = np.random.default_rng(V * 1000 + K)
+    case = _random_case(rng, 157, V, K, min(vocab, 4 * K))
+    _check(*case, vocab=vocab)
+    _check(*case, vocab=vocab, empty_policy=0, k_cap=max(1, K - 5))
     _check(*case, vocab=vocab, rank=False)
 
 
@@ -139,11 +157,12 @@ def test_out_of_vocab_ids_are_counted_and_skipped():
     assert res.union.cpu().tolist() == [[4, 5]]
 
 
-@pytest.mark.parametrize("V,K,vocab", [(31, 20, 3706), (8, 12, 3706), (31, 20, 20000), (3, 64, 50)])
+@pytest.mark.parametrize("V,K,vocab", [(31, 20, 3706), (8, 12, 3706), (31, 20, 20000), (3, 64, 50), (70, 20, 3706)])
 def test_foreign_ids_in_the_neutral_list_count_once_per_user(V, K, vocab):
     """Ids outside [0, vocab) are skipped wherever they stand and counted once per list row: a neutral row
-    belongs to the user, not to each of its V pairs.  Every kernel family (warp, register, table, compare)
-    must report the same number for the same input."""
+    belongs to the user, not to each of its V pairs (nor to each chunk of 32 variants the warp kernel is
+    launched for).  Every kernel family (warp, register, table, compare) must report the same number for the
+    same input."""
     rng = np.random.default_rng(V + K)
     U = 97
     neutral, nlen, lists, lens = _random_case(rng, U, V, K, min(vocab, 60))
@@ -174,16 +193,17 @@ def test_tail_tiles_and_tiny_inputs():
 def test_unaligned_views_take_the_plain_load_path():
     rng = np.random.default_rng(13)
     from fairness_llm_replication_b200 import ops
-    neutral, nlen, lists, lens = _random_case(rng, 41, 31, 10, 3706)
     dev = torch.device("cuda", 0)
     def off(a):                      # same data at a 4-byte offset: not 16-byte aligned
         flat = torch.empty(a.size + 1, dtype=torch.int32, device=dev)
         flat[1:] = torch.from_numpy(a.ravel()).to(dev)
         return flat[1:].view(a.shape)
-    res = ops.list_metrics(off(neutral), off(nlen), off(lists), off(lens), vocab=3706, want_union=True)
-    want = O.list_metrics(neutral, nlen, lists, lens)
-    assert np.array_equal(res.inter.cpu().numpy(), want["inter"])
-    np.testing.assert_allclose(res.prag.cpu().numpy(), want["prag"], rtol=RTOL)
+    for V, K in ((31, 10), (40, 10), (70, 33)):          # one launch; chunks of 32 variants, even and odd K
+        neutral, nlen, lists, lens = _random_case(rng, 41, V, K, 3706)
+        res = ops.list_metrics(off(neutral), off(nlen), off(lists), off(lens), vocab=3706, want_union=True)
+        want = O.list_metrics(neutral, nlen, lists, lens)
+        assert np.array_equal(res.inter.cpu().numpy(), want["inter"])
+        np.testing.assert_allclose(res.prag.cpu().numpy(), want["prag"], rtol=RTOL)
 
 
 def test_synthetic_config2_full_size_matches_oracle():
