@@ -550,6 +550,15 @@ __global__ void __launch_bounds__(NT, 2) list_metrics_reg_kernel(const LmParams 
 // Positions past a row's length hold spare ids (vocab + 1 + position): private bits, table entries
 // that read "absent"; each one counts as a miss that follows every hit, which is subtracted at the end.
 // ---------------------------------------------------------------------------------------
+// Shared-memory address of the word of a lane's bit set that holds bit `idx` (sets are laid out [word][lane],
+// base = the lane's word 0): written as a shift and a multiply-add so that it stays two instructions (the
+// compiler's own form, (idx * 4 & ~127) + base, is three).
+__device__ __forceinline__ uint32_t word_addr32(uint32_t base, unsigned idx) {
+    uint32_t a;
+    asm("{\n\t.reg .u32 w;\n\tshr.u32 w, %2, 5;\n\tmad.lo.u32 %0, w, 128, %1;\n\t}" : "=r"(a) : "r"(base), "r"(idx));
+    return a;
+}
+
 __device__ __forceinline__ uint64_t shl64_clamped(uint64_t v, unsigned amount) {   // amount may be 64 (-> 0)
     uint64_t r;
     asm("shl.b64 %0, %1, %2;" : "=l"(r) : "l"(v), "r"(amount));
@@ -755,9 +764,11 @@ __global__ void __launch_bounds__(NT, 2) list_metrics_warp_kernel(const LmParams
 
         // ---- rank table: tab[id] = 63 - (first position of id in the neutral list), 64 = absent ----
         int n_a;
+        unsigned un_pack;       // the two table entries this lane marks, 16 bits each, kept for the un-mark at the end
         {
             const int Ka = max(0, min(nlen, Kn));
             const unsigned id0 = lane < Ka ? nid0 : vocab, id1 = lane + 32 < Ka ? nid1 : vocab;
+            un_pack = min(id0, vocab) | (min(id1, vocab) << 16);        // foreign -> entry `vocab`, which reads absent anyway
             if (v0 == 0) oov += (lane < Ka && id0 >= vocab ? 1 : 0) + (lane + 32 < Ka && id1 >= vocab ? 1 : 0);   // once per user
             const unsigned t0 = TOP - lane, t1 = TOP - 32u - lane;      // t of positions lane and lane + 32 (t1 unused when NARROW)
             if (id1 < vocab) tab[id1] = static_cast<uint8_t>(t1);       // later half first,
@@ -775,11 +786,14 @@ __global__ void __launch_bounds__(NT, 2) list_metrics_warp_kernel(const LmParams
                 __syncwarp();
             } while (again);
         }
-        const unsigned un_id0 = nid0, un_id1 = nid1;       // kept for the un-mark at the end
-        fetch_small(un, nid0, nid1, nlen, blen);            // next user's small inputs: used one iteration from now
+        // Next user's small inputs, used one iteration from now.  Their current values are dead here (the un-mark
+        // keeps its own packed copy), so the loads land in the loop-carried registers themselves: with a copy of
+        // the old ids still alive, the compiler loaded into temporaries and moved them over at the end of this
+        // iteration -- a wait for the loads half an iteration after issuing them (12 % of the K = 20 kernel).
+        fetch_small(un, nid0, nid1, nlen, blen);
 
         // ---- optimistic pass over the row ----
-        char *bits_base = reinterpret_cast<char *>(s_bits + lane);
+        const uint32_t bits32 = smem_u32(s_bits + lane);
         const uint32_t tab32 = smem_u32(tab);
         int below_hi = 0;                       // the two halves' popcounts go to two sums: adds the FMA pipe can take
         uint32_t seen_lo = 0, seen_hi = 0;      // bit TOP - r = neutral rank r was hit
@@ -789,9 +803,9 @@ __global__ void __launch_bounds__(NT, 2) list_metrics_warp_kernel(const LmParams
 #pragma unroll
         for (int j = 0; j < KT; ++j) {
             const unsigned idx = ids[j];                   // in [0, vocab], or a spare
-            unsigned int *wp = reinterpret_cast<unsigned int *>(bits_base + (idx & ~31u) * 4u);
             const uint32_t bit = 1u << (idx & 31u);
-            const uint32_t old = atomicOr(wp, bit);
+            uint32_t old;                                  // the word's address: a shift and a multiply-add
+            asm volatile("atom.shared.or.b32 %0, [%1], %2;" : "=r"(old) : "r"(word_addr32(bits32, idx)), "r"(bit) : "memory");
             repeat |= old & bit;
             unsigned tt;                                   // TOP - rank, TOP + 1 when absent
             asm volatile("ld.shared.u8 %0, [%1];" : "=r"(tt) : "r"(tab32 + idx));   // one 32-bit base: a two-input add
@@ -916,11 +930,11 @@ __global__ void __launch_bounds__(NT, 2) list_metrics_warp_kernel(const LmParams
         __syncwarp();
         {
 #pragma unroll
-            for (int j = 0; j < KT; ++j) *reinterpret_cast<uint32_t *>(bits_base + (ids[j] & ~31u) * 4u) = 0u;
+            for (int j = 0; j < KT; ++j) asm volatile("st.shared.u32 [%0], %1;" :: "r"(word_addr32(bits32, ids[j])), "r"(0u) : "memory");
             s_bits[own_row * 32 + lane] = foreign_bit;
         }
-        if (un_id0 < vocab) tab[un_id0] = static_cast<uint8_t>(ABSENT);
-        if (un_id1 < vocab) tab[un_id1] = static_cast<uint8_t>(ABSENT);
+        tab[un_pack & 0xffffu] = static_cast<uint8_t>(ABSENT);
+        tab[un_pack >> 16] = static_cast<uint8_t>(ABSENT);
         __syncwarp();
         bulk_cur = bulk_next;
     }

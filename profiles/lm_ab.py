@@ -1,6 +1,6 @@
 """A/B timing of the list-metric kernels on one GPU (development aid, not a bench line).
 
-    python profiles/lm_ab.py [--users 300000] [--k 50] [--variants reg,tas]
+    python profiles/lm_ab.py [--users 300000] [--k 50] [--variants reg,warp] [--lib other/libflr_b200.so]
 
 FLR_LM_KERNEL=reg selects the previous register kernel, anything else the current default.
 Outputs of every variant are compared bit for bit with the first one; times are CUDA events over
@@ -27,7 +27,11 @@ def main():
     ap.add_argument("--iters", type=int, default=20)
     ap.add_argument("--variants", default="reg,tas")
     ap.add_argument("--peak", type=float, default=6546.9)
+    ap.add_argument("--lib", default=None, help="another build of libflr_b200.so to time (same-board A/B of two builds)")
     a = ap.parse_args()
+    if a.lib:
+        from fairness_llm_replication_b200 import _lib
+        _lib.LIB_PATH = os.path.abspath(a.lib)
     dev = torch.device("cuda", 0)
     neutral, nlen, lists, lens = ops.synth_lists(20251203, 0, a.users, a.v, a.k, a.vocab, dev)
     pairs = a.users * a.v
@@ -56,7 +60,7 @@ def main():
         gbs = pairs * bytes_per_pair / (ms * 1e-3) / 1e9
         print(json.dumps({"variant": name, "users": a.users, "K": a.k, "ms": round(ms, 4),
                           "GBps": round(gbs, 1), "frac_of_measured_hbm": round(gbs / a.peak, 4),
-                          "identical_to_first": same}))
+                          "identical_to_first": same, "lib": os.path.basename(os.path.dirname(os.path.abspath(a.lib))) if a.lib else "in-tree"}))
 
 
 if __name__ == "__main__":
