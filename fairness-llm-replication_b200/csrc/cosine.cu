@@ -289,7 +289,36 @@ __global__ void __launch_bounds__(TMA_THREADS, 1) cosine_tma_kernel(const CosTma
             const int first = static_cast<int>((warp + TMA_CONSUMER_WARPS - (it % TMA_CONSUMER_WARPS)) % TMA_CONSUMER_WARPS);
             double av[NC][4];
             double na = 0.0;
-            if constexpr (FAST) {
+            if (V == 1) {
+                // calibration form (one counterfactual row per anchor): a warp takes one (a, b) pair at a time, so
+                // a 16-user stage keeps all sixteen warps busy; its three sums go through one transposed butterfly
+                const int nu = static_cast<int>(min(static_cast<int64_t>(G), p.U - u0));
+                for (int row = first; row < nu; row += TMA_CONSUMER_WARPS) {
+                    const float *arow = sa + static_cast<size_t>(row) * D, *brow = sb + static_cast<size_t>(row) * D;
+                    double acc = 0.0, d = 0.0, n = 0.0;
+#pragma unroll
+                    for (int c = 0; c < NC; ++c) {
+                        const int ch = lane + 32 * c;
+                        float4 qa = make_float4(0.f, 0.f, 0.f, 0.f), qb = qa;
+                        if (FAST || ch < nchunk) {
+                            qa = *reinterpret_cast<const float4 *>(arow + 4 * ch);
+                            qb = *reinterpret_cast<const float4 *>(brow + 4 * ch);
+                        }
+                        av[c][0] = qa.x; av[c][1] = qa.y; av[c][2] = qa.z; av[c][3] = qa.w;
+#pragma unroll
+                        for (int e = 0; e < 4; ++e) acc = fma(av[c][e], av[c][e], acc);
+                        fma4(av[c], qb, d, n);
+                    }
+                    const double v4[4] = {d, n, acc, 0.0};
+                    const double y = reduce4_transposed(v4, lane);          // lanes 0-7: dot, 8-15: |b|^2, 16-23: |a|^2
+                    const double nb_all = __shfl_sync(0xffffffffu, y, 8), na_all = __shfl_sync(0xffffffffu, y, 16);
+                    if (lane == 0) {
+                        const float sc = score_from(y, na_all, nb_all);
+                        p.out[u0 + row] = sc;
+                        if (do_hist) atomicAdd(&s_hist[select_key::key_f32(sc) >> 21], 1u);
+                    }
+                }
+            } else if constexpr (FAST) {
                 // batches never straddle users: user slot = batch / pub, rows (batch % pub) * 4 .. + 3
                 const int nu = static_cast<int>(min(static_cast<int64_t>(G), p.U - u0));
                 const int pub = (V + 3) >> 2;                  // batches per user
@@ -344,35 +373,6 @@ __global__ void __launch_bounds__(TMA_THREADS, 1) cosine_tma_kernel(const CosTma
                     const int r = r0 + (lane >> 3);
                     if ((lane & 7) == 0 && r < V) {
                         p.out[(u0 + slot) * V + r] = sc;
-                        if (do_hist) atomicAdd(&s_hist[select_key::key_f32(sc) >> 21], 1u);
-                    }
-                }
-            } else if (V == 1) {
-                // calibration form (one counterfactual row per anchor): a warp takes one (a, b) pair at a time, so
-                // a 16-user stage keeps all sixteen warps busy; its three sums go through one transposed butterfly
-                const int nu = static_cast<int>(min(static_cast<int64_t>(G), p.U - u0));
-                for (int row = first; row < nu; row += TMA_CONSUMER_WARPS) {
-                    const float *arow = sa + static_cast<size_t>(row) * D, *brow = sb + static_cast<size_t>(row) * D;
-                    double acc = 0.0, d = 0.0, n = 0.0;
-#pragma unroll
-                    for (int c = 0; c < NC; ++c) {
-                        const int ch = lane + 32 * c;
-                        float4 qa = make_float4(0.f, 0.f, 0.f, 0.f), qb = qa;
-                        if (ch < nchunk) {
-                            qa = *reinterpret_cast<const float4 *>(arow + 4 * ch);
-                            qb = *reinterpret_cast<const float4 *>(brow + 4 * ch);
-                        }
-                        av[c][0] = qa.x; av[c][1] = qa.y; av[c][2] = qa.z; av[c][3] = qa.w;
-#pragma unroll
-                        for (int e = 0; e < 4; ++e) acc = fma(av[c][e], av[c][e], acc);
-                        fma4(av[c], qb, d, n);
-                    }
-                    const double v4[4] = {d, n, acc, 0.0};
-                    const double y = reduce4_transposed(v4, lane);          // lanes 0-7: dot, 8-15: |b|^2, 16-23: |a|^2
-                    const double nb_all = __shfl_sync(0xffffffffu, y, 8), na_all = __shfl_sync(0xffffffffu, y, 16);
-                    if (lane == 0) {
-                        const float sc = score_from(y, na_all, nb_all);
-                        p.out[u0 + row] = sc;
                         if (do_hist) atomicAdd(&s_hist[select_key::key_f32(sc) >> 21], 1u);
                     }
                 }
