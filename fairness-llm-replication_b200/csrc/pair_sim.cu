@@ -62,17 +62,16 @@ __global__ void __launch_bounds__(256) normalize_rows_bf16_kernel(const float *_
 #pragma unroll
                 for (int off = 16; off >= 1; off >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, off);
                 const double n = sqrt(ss);
-                const double inv = n > 0.0 ? 1.0 / n : 0.0;
+                const float inv = n > 0.0 ? static_cast<float>(1.0 / n) : 0.0f;
 #pragma unroll
                 for (int c = 0; c < NC; ++c) {
                     const int ch = lane + 32 * c;
                     if (ch < nchunk) {
-                        // one fp64 division per row; x * (1/n) differs from x / n by < 2^-52 relative, which
-                        // the rounding to fp32 and then bf16 absorbs
-                        const float y0 = static_cast<float>(static_cast<double>(q[i][c].x) * inv);
-                        const float y1 = static_cast<float>(static_cast<double>(q[i][c].y) * inv);
-                        const float y2 = static_cast<float>(static_cast<double>(q[i][c].z) * inv);
-                        const float y3 = static_cast<float>(static_cast<double>(q[i][c].w) * inv);
+                        // one fp64 division per row, then fp32 products: x * fp32(1/n) is within 1.2e-7 relative
+                        // of x / n, 2^-15 of a bf16 step -- the rounding to bf16 differs from the exact quotient's
+                        // for about 3 elements in 10^5, by one bf16 step (the fp64 product and its conversion
+                        // back cost two more conversion-pipe instructions per element, which bounded the kernel)
+                        const float y0 = q[i][c].x * inv, y1 = q[i][c].y * inv, y2 = q[i][c].z * inv, y3 = q[i][c].w * inv;
                         __nv_bfloat162 lo = __floats2bfloat162_rn(y0, y1), hi = __floats2bfloat162_rn(y2, y3);
                         uint2 pk;
                         pk.x = *reinterpret_cast<uint32_t *>(&lo);
