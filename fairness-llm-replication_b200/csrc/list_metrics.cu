@@ -655,6 +655,7 @@ __global__ void __launch_bounds__(NT, 2) list_metrics_warp_kernel(const LmParams
 
     const int64_t n_warps = static_cast<int64_t>(gridDim.x) * WK_WARPS;
     const bool live = lane < V;
+    const int idle_row = live ? lane : (lane & 15) < V ? (lane & 15) : 0;     // the staged row a lane copies out
     const int rs = wk_row_stride(K);                     // words between staged rows
     const bool padded = rs != K, vec4 = (K & 3) == 0;    // padded rows are copied one by one, each by its lane
     // user_bytes: what one launch copies per user; a user's rows are user_stride apart in memory
@@ -727,9 +728,12 @@ __global__ void __launch_bounds__(NT, 2) list_metrics_warp_kernel(const LmParams
             __syncwarp();
         }
         unsigned ids[KT];
-        const int Kb = live ? max(0, min(blen, Kn)) : K;       // an idle lane redoes lane 0's row; nothing of it is kept
+        const int Kb = live ? max(0, min(blen, Kn)) : K;       // an idle lane redoes another lane's row; nothing of it is kept
         {
-            const int32_t *row = reinterpret_cast<const int32_t *>(s_stage + delta) + (live ? lane : 0) * rs;
+            // An idle lane reads the row sixteen lanes down: rows 16 apart start on the same banks (the stride is
+            // even), and that row is read by the other half of the warp -- no bank conflict in the idle lane's own
+            // half.  (Row 0, the obvious choice, sits on lane 16's banks: one more wavefront per load for V = 31.)
+            const int32_t *row = reinterpret_cast<const int32_t *>(s_stage + delta) + idle_row * rs;
             if (vec4) {                              // K % 4 == 0: rows are 16-byte aligned, whole 128-bit chunks
 #pragma unroll
                 for (int j0 = 0; j0 < KT; j0 += 4) {
