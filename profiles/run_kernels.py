@@ -39,6 +39,14 @@ def main():
     # K = 20 list metrics at an HBM-resident size
     n2, nl2, l2, ln2 = ops.synth_lists(pipeline.SEED, 0, 500000, 31, 20, 3706, dev)
     ops.list_metrics(n2, nl2, l2, ln2, vocab=3706)
+    del n2, nl2, l2, ln2
+    # config 3: the calibration form of the cosine kernel, 1M pairs of 384-d rows
+    ea, eb = ops.synth_embeddings(pipeline.SEED, 0, 1_000_000, 1, 384, dev)
+    ops.cosine_nonconformity(ea, eb)
+    del ea, eb
+    # more than 32 variants per user: the warp kernel once per chunk of 32 (two launches here)
+    n3, nl3, l3, ln3 = ops.synth_lists(pipeline.SEED, 0, 100000, 64, 50, 3706, dev)
+    ops.list_metrics(n3, nl3, l3, ln3, vocab=3706)
     torch.cuda.synchronize()
     print("done")
 
