@@ -19,7 +19,8 @@ def _emb(rng, U, V, D, sig_hi=0.6):
 
 
 @pytest.mark.parametrize("U,V,D", [(301, 31, 384), (64, 1, 384), (50, 33, 128), (40, 64, 260), (17, 2, 1024),
-                                   (9, 5, 4), (1000, 31, 384), (23, 124, 384), (150, 31, 256), (5, 300, 128)])
+                                   (9, 5, 4), (1000, 31, 384), (23, 124, 384), (150, 31, 256), (5, 300, 128),
+                                   (20000, 1, 128), (5000, 1, 256), (333, 1, 200), (41, 1, 1024), (70000, 1, 384)])
 def test_cosine_matches_oracle(U, V, D):
     from fairness_llm_replication_b200 import ops
     rng = np.random.default_rng(U + V + D)

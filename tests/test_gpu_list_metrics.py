@@ -109,6 +109,62 @@ def test_random_shapes_against_the_oracle():
         _check(*case, vocab=vocab, k_cap=k_cap, empty_policy=int(rng.integers(0, 2)), rank=bool(rng.random() < 0.7))
 
 
+def _fuzz_case(rng):
+    """One random shape with everything that has ever mattered turned on at random: vocabularies on and next
+    to 16-byte boundaries of the rank table, repeats, short and empty rows, foreign ids on either side."""
+    V = int(rng.choice([1, 2, 3, 7, 12, 16, 17, 20, 31, 32, 33, 40, 63, 64, 65, 96, 124, 128, 130]))
+    K = int(rng.choice([1, 2, 5, 9, 10, 11, 16, 19, 20, 21, 31, 32, 33, 40, 48, 50, 51, 56, 62, 63, 64]))
+    vocab = int(rng.choice([K + 3, 64, 90, 255, 256, 257, 2000, 2001, 3706, 4095, 4096, 8191, 16383, 16384, 16385, 50000]))
+    U = int(rng.integers(1, 70))
+    ids = min(vocab, int(rng.choice([max(K // 2, 1), 2 * K, 6 * K, vocab])))
+    neutral, nlen, lists, lens = _random_case(rng, U, V, K, ids)
+    if rng.random() < 0.3:          # foreign ids: negative and beyond the vocabulary
+        bad_l = rng.random(lists.shape) < 0.02
+        bad_n = rng.random(neutral.shape) < 0.03
+        lists = np.where(bad_l, rng.choice([-1, -7, vocab, vocab + 1, vocab + 70, 2 ** 31 - 1], size=lists.shape), lists).astype(np.int32)
+        neutral = np.where(bad_n, rng.choice([-3, vocab, vocab + 64, 2 ** 30], size=neutral.shape), neutral).astype(np.int32)
+    k_cap = None if rng.random() < 0.5 else int(rng.integers(1, K + 1))
+    return (neutral, nlen, lists, lens), dict(vocab=vocab, k_cap=k_cap, empty_policy=int(rng.integers(0, 2)),
+                                              rank=bool(rng.random() < 0.7))
+
+
+def _check_with_foreign_ids(neutral, nlen, lists, lens, vocab, k_cap, empty_policy, rank):
+    """Like _check, for inputs that may hold ids outside [0, vocab): those are skipped wherever they stand and
+    counted in `status`; intersections and unions are checked against Python sets."""
+    U, V, K = lists.shape
+    kc = K if k_cap is None else k_cap
+    ok_n, ok_l = (neutral >= 0) & (neutral < vocab), (lists >= 0) & (lists < vocab)
+    if ok_n.all() and ok_l.all():
+        _check(neutral, nlen, lists, lens, vocab=vocab, k_cap=k_cap, empty_policy=empty_policy, rank=rank)
+        return
+    res = _run(neutral, nlen, lists, lens, vocab=vocab, k_cap=k_cap, empty_policy=empty_policy, rank_metrics=rank)
+    inter, union = res.inter.cpu().numpy(), res.union.cpu().numpy()
+    pos = np.arange(K)
+    in_n = pos[None, :] < np.minimum(nlen, kc)[:, None]
+    in_l = pos[None, None, :] < np.minimum(lens, kc)[:, :, None]
+    assert int(res.status.item()) == int((~ok_n & in_n).sum() + (~ok_l & in_l).sum())
+    for u in range(U):
+        a = {int(x) for x, o, i in zip(neutral[u], ok_n[u], in_n[u]) if o and i}
+        for v in range(V):
+            b = {int(x) for x, o, i in zip(lists[u, v], ok_l[u, v], in_l[u, v]) if o and i}
+            assert inter[u, v] == len(a & b) and union[u, v] == len(a | b), (u, v)
+
+
+def test_fuzz_shapes_against_the_oracle():
+    """Random shapes over every kernel family and plan boundary (FLR_FUZZ_SHAPES of them, default 200; the
+    default takes a few seconds, 3000 have been run).  Foreign-id cases check the counts against Python sets."""
+    import os
+    rng = np.random.default_rng(int(os.environ.get("FLR_FUZZ_SEED", "77")))
+    for i in range(int(os.environ.get("FLR_FUZZ_SHAPES", "200"))):
+        case, kw = _fuzz_case(rng)
+        if kw["rank"] and (kw["k_cap"] or case[2].shape[2]) > 64:
+            kw["rank"] = False
+        try:
+            _check_with_foreign_ids(*case, **kw)
+        except AssertionError as e:
+            raise AssertionError("shape %d: U, V, K = %s, %s: %s" % (i, case[2].shape, kw, e)) from e
+
+
 @pytest.mark.parametrize("V,K,vocab", [(1, 10, 500), (1, 20, 100000), (3, 64, 50), (124, 20, 3706), (5, 12, 70000)])
 def test_compare_kernel_shapes(V, K, vocab):
     """V = 1 pair lists (string API), huge vocabularies and V > 128 go through the compare kernel."""
