@@ -207,6 +207,45 @@ __device__ __forceinline__ float reduce_batch_scores(const double (&x)[8], const
     return score_from(dot, my_na, nb);
 }
 
+// The same, with the anchor row's running |a|^2 reduced alongside: its plain butterfly (16, 8, 4, 2, 1 -- the
+// bits warp_sum() gives) runs step by step beside the batch's, so the two dependency chains hide each other's
+// shuffle latency instead of running one after the other.
+__device__ __forceinline__ float reduce_batch_scores_na(const double (&x)[8], double acc_a, int lane) {
+    double y4[4], y2[2], y1;
+    {
+        const bool hi = lane & 16;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const double keep = hi ? x[k + 4] : x[k], send = hi ? x[k] : x[k + 4];
+            y4[k] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
+        }
+        acc_a += __shfl_xor_sync(0xffffffffu, acc_a, 16);
+    }
+    {
+        const bool hi = lane & 8;
+#pragma unroll
+        for (int k = 0; k < 2; ++k) {
+            const double keep = hi ? y4[k + 2] : y4[k], send = hi ? y4[k] : y4[k + 2];
+            y2[k] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
+        }
+        acc_a += __shfl_xor_sync(0xffffffffu, acc_a, 8);
+    }
+    {
+        const bool hi = lane & 4;
+        const double keep = hi ? y2[1] : y2[0], send = hi ? y2[0] : y2[1];
+        y1 = keep + __shfl_xor_sync(0xffffffffu, send, 4);
+        acc_a += __shfl_xor_sync(0xffffffffu, acc_a, 4);
+    }
+    y1 += __shfl_xor_sync(0xffffffffu, y1, 2);
+    acc_a += __shfl_xor_sync(0xffffffffu, acc_a, 2);
+    y1 += __shfl_xor_sync(0xffffffffu, y1, 1);
+    acc_a += __shfl_xor_sync(0xffffffffu, acc_a, 1);
+    const double other = __shfl_xor_sync(0xffffffffu, y1, 4);
+    const bool is_nb = (lane >> 2) & 1;
+    const double dot = is_nb ? other : y1, nb = is_nb ? y1 : other;
+    return score_from(dot, acc_a, nb);
+}
+
 // Reduce four running sums over the warp with the same transposed xor butterfly (offsets 16, 8 halve the
 // set each lane carries, then 4, 2, 1): lane l ends up with sum number (l >> 3) & 3.  Every addition pairs
 // the operands the plain butterfly would, so each sum has the bits warp_sum() gives it.
@@ -337,12 +376,11 @@ __global__ void __launch_bounds__(TMA_THREADS, 1) cosine_tma_kernel(const CosTma
 #pragma unroll
                             for (int e = 0; e < 4; ++e) acc = fma(av[c][e], av[c][e], acc);
                         }
-                        na = warp_sum(acc);
+                        na = acc;                              // this lane's share; summed over the warp with the batch
                         cur_slot = slot;
                     }
                     const float *srow = sb + static_cast<size_t>(slot) * V * D;
                     double x[8];
-                    const double na_row[4] = {na, na, na, na};
                     if (r0 + 4 <= V) {                         // full batch: twelve independent 128-bit loads
                         float4 q[4][NC];
 #pragma unroll
@@ -369,7 +407,7 @@ __global__ void __launch_bounds__(TMA_THREADS, 1) cosine_tma_kernel(const CosTma
                             x[2 * i] = d; x[2 * i + 1] = n;
                         }
                     }
-                    const float sc = reduce_batch_scores(x, na_row, lane);
+                    const float sc = reduce_batch_scores_na(x, na, lane);
                     const int r = r0 + (lane >> 3);
                     if ((lane & 7) == 0 && r < V) {
                         p.out[(u0 + slot) * V + r] = sc;
