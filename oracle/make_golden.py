@@ -1,7 +1,8 @@
 """Generate tests/golden/reference_golden.json by running the UNMODIFIED reference
 functions from /root/reference/src on seeded inputs.  Run in the build container:
 
-    python -m oracle.make_golden
+    python -m oracle.make_golden                      (everything)
+    python -m oracle.make_golden --append-missing     (only the sections the committed file lacks)
 
 TEST INFRASTRUCTURE ONLY.  The JSON holds inputs and the reference's outputs; floats
 round-trip exactly through ``repr``.  (The reference's demographic-parity distances are summed in the
@@ -45,6 +46,32 @@ def _profiles(genders, ages, occs, repeats):
                 for r in range(repeats):
                     out.append({"id": f"p_{g}_{a}_{o}_{r}", "gender": g, "age": a, "occupation": o})
     return out
+
+
+def aggressive_cases():
+    """a5, second copy: jaccard / measure_fairness of src/phase3_aggressive.py:174-195 (own seed, so that
+    adding this section left every earlier vector as it was)."""
+    agg = ref_loader.load_script_functions("phase3_aggressive.py")
+    rng = random.Random(174195)
+    inputs = [{"g1": [["a"]]}, {"g1": [[]], "g2": [[]]}, {"g1": [], "g2": []}, {"a": [["x"]], "b": [["x"]], "c": [["x"]]},
+              {"m": [["a", "b"], []], "f": [["b", "c"], ["q"]]}]
+    for _ in range(10):
+        n1, n2 = rng.randint(0, 8), rng.randint(0, 8)
+        inputs.append({"male": [_rand_list(rng, 10, p_empty=0.2) for _ in range(n1)],
+                       "female": [_rand_list(rng, 10, p_empty=0.2) for _ in range(n2)]})
+    return {"jaccard": [{"s1": s1, "s2": s2, "jaccard": float(agg.jaccard(set(s1), set(s2)))}
+                        for s1, s2 in [([], []), (["a"], []), ([], ["b"]), (["a", "b"], ["b", "c"]), (["a"], ["a"])]],
+            "measure_fairness": [{"recs_by_group": d, "fairness": float(agg.measure_fairness(d))} for d in inputs]}
+
+
+def append_missing():
+    """Add the sections the committed file does not have yet, leaving the others untouched."""
+    g = json.load(open(OUT))
+    if "aggressive" not in g:
+        g["aggressive"] = aggressive_cases()
+    with open(OUT, "w") as f:
+        json.dump(g, f, indent=0, sort_keys=True)
+    print("updated", OUT)
 
 
 def main():
@@ -294,10 +321,13 @@ def main():
                           "titles": [utils.extract_movie_title(x) for x in utils.parse_recommendation_list(t)]}
                          for t in texts]
 
+    g["aggressive"] = aggressive_cases()
+
     with open(OUT, "w") as f:
         json.dump(g, f, indent=0, sort_keys=True)
     print("wrote", OUT, os.path.getsize(OUT), "bytes")
 
 
 if __name__ == "__main__":
-    main()
+    import sys
+    append_missing() if "--append-missing" in sys.argv else main()

@@ -94,6 +94,18 @@ def measure_fairness(recs_by_group) -> float:
     return (pair_avg * 0.6) + (jaccard(all1, all2) * 0.4)
 
 
+def measure_fairness_aggressive(recs_by_group) -> float:
+    """src/phase3_aggressive.py:181-195 -- the earlier form of the same helper: exactly two groups or 0.5;
+    mean over ALL aligned positions of J(g1[i], g2[i]) (a position with an empty list counts 0.0); no
+    position -> 0.5.  Its ``jaccard`` (src/phase3_aggressive.py:174-179) is the one above."""
+    groups = list(recs_by_group.keys())
+    if len(groups) != 2:
+        return 0.5
+    g1, g2 = recs_by_group[groups[0]], recs_by_group[groups[1]]
+    sims = [jaccard(set(a), set(b)) for a, b in zip(g1, g2)]
+    return np.mean(sims) if sims else 0.5
+
+
 def calculate_conformal_thresholds(calibration_data, alpha: float = 0.1) -> Dict[str, float]:
     """src/phase3_facter_mitigation.py:152-182 -- per group, sorted scores at index
     ceil((n+1)(1-alpha))-1 clamped to [0, n-1]; empty group -> 0.5."""

@@ -418,6 +418,15 @@ def test_dropin_phase3_final(golden):
         assert float(fin.measure_fairness(c["recs_by_group"])) == c["fairness"]
 
 
+def test_dropin_phase3_aggressive(golden):
+    """The earlier copy of the two helpers (src/phase3_aggressive.py:174-195): own golden vectors."""
+    from fairness_llm_replication_b200 import phase3_aggressive as agg
+    for c in golden["aggressive"]["jaccard"]:
+        assert agg.jaccard(set(c["s1"]), set(c["s2"])) == c["jaccard"]
+    for c in golden["aggressive"]["measure_fairness"]:
+        assert float(agg.measure_fairness(c["recs_by_group"])) == c["fairness"]
+
+
 def test_pair_jaccard_bitsets():
     from fairness_llm_replication_b200 import ops
     rng = np.random.default_rng(21)

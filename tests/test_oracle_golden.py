@@ -81,6 +81,13 @@ def test_final_jaccard_and_fairness_port(golden):
         assert float(R.measure_fairness(c["recs_by_group"])) == c["fairness"]
 
 
+def test_aggressive_jaccard_and_fairness_port(golden):
+    for c in golden["aggressive"]["jaccard"]:
+        assert R.jaccard(set(c["s1"]), set(c["s2"])) == c["jaccard"]
+    for c in golden["aggressive"]["measure_fairness"]:
+        assert float(R.measure_fairness_aggressive(c["recs_by_group"])) == c["fairness"]
+
+
 def test_conformal_index_rule(golden):
     for c in golden["conformal_index"]:
         assert O.conformal_index(c["n"], c["alpha"]) == c["index"]
