@@ -145,3 +145,35 @@ def measure_quality_preservation(original_recs: Dict, mitigated_recs: Dict) -> D
     avg_overlap = np.mean(overlaps) if overlaps else 0
     return {"average_overlap": avg_overlap, "quality_preservation_pct": avg_overlap * 100,
             "num_comparisons": len(overlaps)}
+
+
+def measure_bias_reduction(original_recs: Dict, mitigated_recs: Dict, profiles: List[Dict]) -> Dict:
+    """Demographic parity by gender before and after mitigation and the relative bias reduction --
+    reference: src/phase3_facter_mitigation.py:280-331 (the phase-3 caller of N1).  Lists are grouped by the
+    profile's gender (ids without a profile and values that are neither a list nor a dict with
+    'recommendations' are skipped, as there); the two parity scores come from the GPU histogram / distance
+    kernels behind ``utils.calculate_demographic_parity``."""
+    profile_dict = {p["id"]: p for p in profiles}
+
+    def organize_recs(recs_dict):
+        by_gender: Dict[str, List[List[str]]] = {}
+        for pid, recs in recs_dict.items():
+            if pid not in profile_dict:
+                continue
+            gender = profile_dict[pid]["gender"]
+            if isinstance(recs, dict) and "recommendations" in recs:
+                rec_list = recs["recommendations"]
+            elif isinstance(recs, list):
+                rec_list = recs
+            else:
+                continue
+            by_gender.setdefault(gender, []).append(rec_list)
+        return by_gender
+
+    original_dp, _ = utils.calculate_demographic_parity(organize_recs(original_recs))
+    mitigated_dp, _ = utils.calculate_demographic_parity(organize_recs(mitigated_recs))
+    original_bias = 1 - original_dp
+    mitigated_bias = 1 - mitigated_dp
+    bias_reduction_rate = (original_bias - mitigated_bias) / original_bias * 100 if original_bias > 0 else 0
+    return {"original_fairness": original_dp, "mitigated_fairness": mitigated_dp, "original_bias": original_bias,
+            "mitigated_bias": mitigated_bias, "bias_reduction_rate": bias_reduction_rate}

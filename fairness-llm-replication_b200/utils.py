@@ -147,6 +147,36 @@ def profile_pair_indices(profiles: List[Dict], differing_attribute: Optional[str
     return np.concatenate(out_i).astype(np.int64), np.concatenate(out_j).astype(np.int64)
 
 
+def _aligned_distributions(p: Dict[Hashable, float], q: Dict[Hashable, float]) -> Tuple[np.ndarray, np.ndarray]:
+    """The reference's preamble (src/utils.py:75-84, :93-100): union of the keys, 1e-10 for a missing key,
+    each side renormalised."""
+    keys = set(list(p.keys()) + list(q.keys()))
+    pa = np.array([p.get(k, 1e-10) for k in keys])
+    qa = np.array([q.get(k, 1e-10) for k in keys])
+    return pa / pa.sum(), qa / qa.sum()
+
+
+def calculate_kl_divergence(p: Dict[Hashable, float], q: Dict[Hashable, float]) -> float:
+    """KL(p || q) in nats between two distributions given as dicts -- reference: src/utils.py:70-87
+    (``scipy.stats.entropy(p, q)``).  Host arithmetic: two small dicts are not GPU work; the batched form of
+    the divergences is ``ops.js_distance_matrix`` behind ``calculate_demographic_parity``."""
+    pa, qa = _aligned_distributions(p, q)
+    pa, qa = pa / np.sum(pa), qa / np.sum(qa)           # scipy.stats.entropy normalises once more
+    return float(np.sum(np.where(pa > 0, pa * np.log(np.where(pa > 0, pa, 1.0) / qa), 0.0)))
+
+
+def calculate_js_divergence(p: Dict[Hashable, float], q: Dict[Hashable, float]) -> float:
+    """Jensen-Shannon DISTANCE (the square root of the divergence, natural log -- what
+    ``scipy.spatial.distance.jensenshannon`` returns) between two distributions given as dicts --
+    reference: src/utils.py:89-102.  Host arithmetic, as ``calculate_kl_divergence``."""
+    pa, qa = _aligned_distributions(p, q)
+    pa, qa = pa / np.sum(pa), qa / np.sum(qa)
+    m = (pa + qa) / 2.0
+    left = np.where(pa > 0, pa * np.log(np.where(pa > 0, pa, 1.0) / m), 0.0)
+    right = np.where(qa > 0, qa * np.log(np.where(qa > 0, qa, 1.0) / m), 0.0)
+    return float(np.sqrt((np.sum(left) + np.sum(right)) / 2.0))
+
+
 def calculate_demographic_parity(recommendations_by_group: Dict[str, List[List[str]]],
                                  genre_mapping: Optional[Dict[str, List[str]]] = None,
                                  _encoded: Optional[encode.EncodedRecommendations] = None) -> Tuple[float, Dict]:

@@ -64,11 +64,47 @@ def aggressive_cases():
             "measure_fairness": [{"recs_by_group": d, "fairness": float(agg.measure_fairness(d))} for d in inputs]}
 
 
+def divergence_and_bias_reduction_cases():
+    """utils.calculate_kl_divergence / calculate_js_divergence (src/utils.py:70-102) and
+    phase3_facter_mitigation.measure_bias_reduction (:280-331), own seed."""
+    utils = ref_loader.load("utils")
+    p3 = ref_loader.load("phase3_facter_mitigation")
+    rng = random.Random(280331)
+
+    def dist(n):
+        keys = rng.sample(TITLES, n)
+        w = [rng.random() + 0.01 for _ in keys]
+        return {k: x / sum(w) for k, x in zip(keys, w)}
+    pairs = [({"a": 1.0}, {"a": 1.0}), ({"a": 1.0}, {"b": 1.0}), ({"a": 0.5, "b": 0.5}, {"a": 0.9, "b": 0.1}),
+             ({"a": 2, "b": 6}, {"b": 1, "c": 3})]                      # unnormalised inputs are renormalised
+    pairs += [(dist(rng.randint(1, 12)), dist(rng.randint(1, 12))) for _ in range(10)]
+    div = [{"p": p, "q": q, "kl": float(utils.calculate_kl_divergence(p, q)),
+            "js": float(utils.calculate_js_divergence(p, q))} for p, q in pairs]
+    cases = []
+    for n in (0, 1, 6, 30):
+        profs = [{"id": f"u{i}", "gender": rng.choice(["male", "female", "non-binary"]), "age": "25-34",
+                  "occupation": "other"} for i in range(n)]
+        def recs(p_dict):
+            out = {}
+            for p in profs:
+                r = _rand_list(rng, 10, p_empty=0.1, p_dup=0.2)
+                x = rng.random()
+                out[p["id"]] = {"recommendations": r} if x < p_dict else r if x < 0.95 else "n/a"
+            out["ghost"] = ["Heat"]                                      # no such profile: skipped
+            return out
+        o, m = recs(0.5), recs(0.3)
+        r = p3.measure_bias_reduction(o, m, profs)
+        cases.append({"profiles": profs, "original": o, "mitigated": m, "result": {k: float(v) for k, v in r.items()}})
+    return {"divergences": div, "bias_reduction": cases}
+
+
 def append_missing():
     """Add the sections the committed file does not have yet, leaving the others untouched."""
     g = json.load(open(OUT))
     if "aggressive" not in g:
         g["aggressive"] = aggressive_cases()
+    if "bias_reduction" not in g:
+        g.update(divergence_and_bias_reduction_cases())
     with open(OUT, "w") as f:
         json.dump(g, f, indent=0, sort_keys=True)
     print("updated", OUT)
@@ -322,6 +358,7 @@ def main():
                          for t in texts]
 
     g["aggressive"] = aggressive_cases()
+    g.update(divergence_and_bias_reduction_cases())
 
     with open(OUT, "w") as f:
         json.dump(g, f, indent=0, sort_keys=True)

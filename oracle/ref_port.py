@@ -170,6 +170,43 @@ def calculate_js_divergence(p: Dict[str, float], q: Dict[str, float]) -> float:
     return float(_js_distance(pa / pa.sum(), qa / qa.sum()))
 
 
+def calculate_kl_divergence(p: Dict[str, float], q: Dict[str, float]) -> float:
+    """src/utils.py:70-87 -- KL(p || q) in nats over the union of the two key sets, a missing key counting
+    1e-10, each side renormalised first (scipy.stats.entropy(p, q) renormalises again: a no-op here)."""
+    keys = set(list(p.keys()) + list(q.keys()))
+    pa = np.array([p.get(k, 1e-10) for k in keys])
+    qa = np.array([q.get(k, 1e-10) for k in keys])
+    pa, qa = pa / pa.sum(), qa / qa.sum()
+    pa, qa = pa / np.sum(pa), qa / np.sum(qa)
+    return float(np.sum(np.where(pa > 0, pa * np.log(np.where(pa > 0, pa, 1.0) / qa), 0.0)))
+
+
+def measure_bias_reduction(original_recs, mitigated_recs, profiles) -> Dict:
+    """src/phase3_facter_mitigation.py:280-331 -- demographic parity by gender before / after, and the
+    relative reduction of (1 - parity) in percent (0 when there was no bias to reduce)."""
+    prof = {p["id"]: p for p in profiles}
+
+    def organize(recs_dict):
+        out: Dict[str, list] = {}
+        for pid, recs in recs_dict.items():
+            if pid not in prof:
+                continue
+            if isinstance(recs, dict) and "recommendations" in recs:
+                lst = recs["recommendations"]
+            elif isinstance(recs, list):
+                lst = recs
+            else:
+                continue
+            out.setdefault(prof[pid]["gender"], []).append(lst)
+        return out
+
+    o, _ = calculate_demographic_parity(organize(original_recs))
+    m, _ = calculate_demographic_parity(organize(mitigated_recs))
+    ob, mb = 1 - o, 1 - m
+    return {"original_fairness": o, "mitigated_fairness": m, "original_bias": ob, "mitigated_bias": mb,
+            "bias_reduction_rate": (ob - mb) / ob * 100 if ob > 0 else 0}
+
+
 def _js_distance(p: np.ndarray, q: np.ndarray) -> float:
     """scipy.spatial.distance.jensenshannon(p, q) restated (scipy 1.x): normalise, m = (p+q)/2,
     sqrt((KL(p||m) + KL(q||m)) / 2)."""

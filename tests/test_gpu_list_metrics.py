@@ -480,6 +480,20 @@ def test_dropin_demographic_parity(golden):
         assert float(s2) == float(score)
 
 
+def test_dropin_divergences_and_bias_reduction(golden):
+    """utils.calculate_kl_divergence / calculate_js_divergence (host helpers, src/utils.py:70-102) and the phase-3
+    caller of demographic parity, measure_bias_reduction (src/phase3_facter_mitigation.py:280-331)."""
+    from fairness_llm_replication_b200 import phase3_facter_mitigation as p3, utils
+    for c in golden["divergences"]:
+        assert utils.calculate_kl_divergence(c["p"], c["q"]) == pytest.approx(c["kl"], rel=1e-12, abs=1e-15)
+        assert utils.calculate_js_divergence(c["p"], c["q"]) == pytest.approx(c["js"], rel=1e-12, abs=1e-8)
+    for c in golden["bias_reduction"]:
+        got = p3.measure_bias_reduction(c["original"], c["mitigated"], c["profiles"])
+        assert set(got) == set(c["result"])
+        for k, v in c["result"].items():
+            assert float(got[k]) == pytest.approx(v, rel=1e-9, abs=1e-12)
+
+
 def test_dropin_equal_opportunity(golden):
     """N4: bit-identical to the reference (integer counts from the GPU, the reference's own float ops)."""
     from fairness_llm_replication_b200 import utils, phase1_bias_detection as p1

@@ -88,6 +88,19 @@ def test_aggressive_jaccard_and_fairness_port(golden):
         assert float(R.measure_fairness_aggressive(c["recs_by_group"])) == c["fairness"]
 
 
+def test_divergence_and_bias_reduction_port(golden):
+    """KL / JS helpers (src/utils.py:70-102) and measure_bias_reduction (src/phase3_facter_mitigation.py:280):
+    the reference sums in the order of a Python set, so 1e-12 relative rather than equality."""
+    for c in golden["divergences"]:
+        assert R.calculate_kl_divergence(c["p"], c["q"]) == pytest.approx(c["kl"], rel=1e-12, abs=1e-15)
+        assert R.calculate_js_divergence(c["p"], c["q"]) == pytest.approx(c["js"], rel=1e-12, abs=1e-8)
+    for c in golden["bias_reduction"]:
+        got = R.measure_bias_reduction(c["original"], c["mitigated"], c["profiles"])
+        assert set(got) == set(c["result"])
+        for k, v in c["result"].items():
+            assert float(got[k]) == pytest.approx(v, rel=1e-9, abs=1e-12)
+
+
 def test_conformal_index_rule(golden):
     for c in golden["conformal_index"]:
         assert O.conformal_index(c["n"], c["alpha"]) == c["index"]
