@@ -78,7 +78,8 @@ def test_static_scratch_entry_matches_regular_entry_twice_in_a_row():
     flr_list_metrics.  The second call reuses the array the first one wrote into."""
     shapes = [dict(seed=1, U=5003, V=31, K=50, vocab=3706, k_cap=50, policy=1, rank=1),    # table kernel
               dict(seed=2, U=777, V=31, K=20, vocab=3706, k_cap=10, policy=0, rank=1),     # fewer CTAs, stale tail
-              dict(seed=3, U=20000, V=1, K=12, vocab=900, k_cap=12, policy=1, rank=0)]     # compare kernel
+              dict(seed=3, U=20000, V=1, K=12, vocab=900, k_cap=12, policy=1, rank=0),     # compare kernel
+              dict(seed=4, U=901, V=70, K=50, vocab=3706, k_cap=50, policy=1, rank=1)]     # three chunks of variants
     for s in shapes:
         tensors = _inputs(s["seed"], s["U"], s["V"], s["K"], s["vocab"])
         args = (tensors, s["U"], s["V"], s["K"], s["vocab"], s["k_cap"], s["policy"], s["rank"])
