@@ -5,11 +5,11 @@
 // rank in the neutral list, per (user, variant) row a private `vocab`-bit set that collapses repeated
 // ids exactly as the reference's set() does; PRAG*'s pair count is a running 64-bit mask of the neutral
 // ranks already seen:
-//   warp kernel     17 <= V <= 128, K <= 64 (the benchmark shapes): one warp per user, one lane per variant,
+//   warp kernel     4 <= V <= 128 (V * K >= 80), K <= 64 (the benchmark shapes): one warp per user, one lane per variant,
 //                   no block barrier, an optimistic test-and-set main loop with an exact warp-cooperative
 //                   redo of the rare rows that hold a repeat or a foreign id (described at its definition);
 //                   more than 32 variants run as one launch per chunk of 32;
-//   register kernel V < 17, K <= 62: one thread per pair, one CTA per tile of users, rows in
+//   register kernel V = 2, 3 and short rows of few variants, K <= 62: one thread per pair, one CTA per tile of users, rows in
 //                   registers, tiles staged by bulk TMA copies one tile ahead;
 //   table kernel    K = 63, 64: the same tile structure with the row read from shared memory;
 //   compare kernel  everything else (V = 1 pair lists of the string API, vocabularies beyond 16384 ids,
@@ -1132,7 +1132,11 @@ Plan make_plan(int64_t U, int V, int K, int k_cap, int vocab) {
         // so the bulk copies' alignment arithmetic is that of the one-chunk case)
         const bool warp_fits = wcap != 0 && !(pick && pick[0] == 'r') &&
                                wk_layout(Vw, K, wcap, vocab).total <= static_cast<size_t>(226 * 1024);
-        if (warp_fits && V >= 17) {
+        // Fewer than 17 variants leave lanes idle, but a warp's time per user hardly depends on V, while the tile
+        // kernels' grows with the pairs: measured, the warp kernel is ahead from four variants of 20 items up
+        // (V=4, K=20: 1.7x; V=16, K=50: 1.8x; V=8..16, K=20: 5-8 %), behind at V=3, K=10 (0.7x).
+        // FLR_LM_KERNEL=w / =r force one or the other for A/B timing.
+        if (warp_fits && (V >= 17 || (V >= 4 && V * K >= 80) || (pick && pick[0] == 'w'))) {
             plan_warp();
             return pl;
         }

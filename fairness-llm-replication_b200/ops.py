@@ -143,7 +143,7 @@ def list_metrics_kernel_name(V: int, K: int, vocab: int, k_cap: Optional[int] = 
         warp_bytes = 16 + a16(Vw * rs * 4 + 16) + a16(vocab + 65) + a16(((vocab >> 5) + 3) * 128) + a16(wcap * 4)
         warp_fits = bool(wcap) and a16((2 * wcap + 1) * 8) + 4 * ((warp_bytes + 127) & ~127) <= 226 * 1024
         warp_name = "list_metrics_warp_kernel<%d,%d,%d>" % (wcap, r, 1 if V > 32 else 0)
-        if warp_fits and V >= 17:
+        if warp_fits and (V >= 17 or (V >= 4 and V * K >= 80)):
             return warp_name
         vocab_pad, W = (vocab + 16) & ~15, (vocab + 31) // 32
 

@@ -53,8 +53,15 @@ def _random_case(rng, U, V, K, vocab, p_dup=0.3):
     return neutral, nlen, lists, lens
 
 
+@pytest.mark.parametrize("forced", ["", "r"])
 @pytest.mark.parametrize("V,K", [(31, 20), (31, 50), (31, 64), (32, 10), (7, 13), (16, 3), (2, 1), (64, 8)])
-def test_table_kernel_random(V, K):
+def test_table_kernel_random(V, K, forced, monkeypatch):
+    """Every shape twice: with the planner's own choice, and with FLR_LM_KERNEL=r, which keeps the tile kernels
+    (register / table) in use for shapes the warp kernel would otherwise take."""
+    if forced:
+        monkeypatch.setenv("FLR_LM_KERNEL", forced)
+    else:
+        monkeypatch.delenv("FLR_LM_KERNEL", raising=False)
     rng = np.random.default_rng(V * 100 + K)
     vocab = 3706 if K > 8 else 40            # small vocab => many duplicates and hits
     case = _random_case(rng, 203, V, K, vocab)
@@ -157,12 +164,16 @@ def test_fuzz_shapes_against_the_oracle():
     rng = np.random.default_rng(int(os.environ.get("FLR_FUZZ_SEED", "77")))
     for i in range(int(os.environ.get("FLR_FUZZ_SHAPES", "200"))):
         case, kw = _fuzz_case(rng)
+        forced = rng.random() < 0.3                      # keep the tile kernels in the mix
+        os.environ["FLR_LM_KERNEL"] = "r" if forced else ""
         if kw["rank"] and (kw["k_cap"] or case[2].shape[2]) > 64:
             kw["rank"] = False
         try:
             _check_with_foreign_ids(*case, **kw)
         except AssertionError as e:
-            raise AssertionError("shape %d: U, V, K = %s, %s: %s" % (i, case[2].shape, kw, e)) from e
+            raise AssertionError("shape %d: U, V, K = %s, %s, tile kernels forced: %s: %s" % (i, case[2].shape, kw, forced, e)) from e
+        finally:
+            os.environ.pop("FLR_LM_KERNEL", None)
 
 
 @pytest.mark.parametrize("V,K,vocab", [(1, 10, 500), (1, 20, 100000), (3, 64, 50), (124, 20, 3706), (5, 12, 70000)])
